@@ -1,0 +1,403 @@
+/*
+ * zk_ctx.cu — context management and the extern "C" entry points of libzkbatch.so
+ * (declared in include/zkbatch.h).  The *_dev entry points take device pointers; the
+ * *_host entry points stage host buffers through context-owned device memory and hand
+ * back context-owned pinned host columns.  There is no CPU codec anywhere in here:
+ * without a CUDA device zkb_ctx_create fails and nothing else is callable.
+ */
+#include <new>
+#include <stdlib.h>
+
+#include "zk_internal.h"
+
+/* the library is built with -fvisibility=hidden: only the ABI of include/zkbatch.h is exported */
+#define ZKB_EXPORT extern "C" __attribute__((visibility("default")))
+
+int zk_ensure(zkb_ctx *ctx, void **p, size_t *have, size_t need, int pinned_host)
+{
+	if (*have >= need && *p) return ZKB_OK;
+	/* grow geometrically so a stream of slightly larger batches does not reallocate each time */
+	size_t want = need + need / 4 + 4096;
+	if (*p) {
+		if (pinned_host) cudaFreeHost(*p); else cudaFree(*p);
+		*p = NULL; *have = 0;
+	}
+	cudaError_t e = pinned_host ? cudaHostAlloc(p, want, cudaHostAllocDefault) : cudaMalloc(p, want);
+	if (e != cudaSuccess) {
+		/* retry with the exact size before giving up */
+		(void)cudaGetLastError();
+		want = need;
+		e = pinned_host ? cudaHostAlloc(p, want, cudaHostAllocDefault) : cudaMalloc(p, want);
+	}
+	if (e != cudaSuccess) {
+		(void)cudaGetLastError();
+		*p = NULL;
+		snprintf(ctx->err, sizeof (ctx->err), "allocation of %zu %s bytes failed: %s", want,
+		    pinned_host ? "pinned host" : "device", cudaGetErrorString(e));
+		return ZKB_ENOMEM;
+	}
+	*have = want;
+	return ZKB_OK;
+}
+
+ZKB_EXPORT int zkb_ctx_create(int device_id, zkb_ctx **out)
+{
+	if (!out) return ZKB_EINVAL;
+	*out = NULL;
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device_id < 0 || device_id >= ndev) {
+		(void)cudaGetLastError();
+		return ZKB_ENODEV;
+	}
+	if (cudaSetDevice(device_id) != cudaSuccess) { (void)cudaGetLastError(); return ZKB_ENODEV; }
+	zkb_ctx *ctx = new (std::nothrow) zkb_ctx();
+	if (!ctx) return ZKB_ENOMEM;
+	memset(ctx, 0, sizeof (*ctx));
+	ctx->device = device_id;
+	strcpy(ctx->err, "");
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) { delete ctx; return ZKB_ENODEV; }
+	ctx->sm_count = prop.multiProcessorCount;
+	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+	    cudaMalloc((void **)&ctx->d_ctrl, sizeof (zk_ctrl)) != cudaSuccess ||
+	    cudaHostAlloc((void **)&ctx->h_ctrl, sizeof (zk_ctrl), cudaHostAllocDefault) != cudaSuccess) {
+		(void)cudaGetLastError();
+		zkb_ctx_destroy(ctx);
+		return ZKB_ENOMEM;
+	}
+	*out = ctx;
+	return ZKB_OK;
+}
+
+ZKB_EXPORT void zkb_ctx_destroy(zkb_ctx *ctx)
+{
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+	if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+	if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
+	if (ctx->h_ctrl) cudaFreeHost(ctx->h_ctrl);
+	if (ctx->d_in) cudaFree(ctx->d_in);
+	if (ctx->d_out) cudaFree(ctx->d_out);
+	if (ctx->h_out) cudaFreeHost(ctx->h_out);
+	if (ctx->h_in) cudaFreeHost(ctx->h_in);
+	delete ctx;
+}
+
+ZKB_EXPORT const char *zkb_last_error(const zkb_ctx *ctx) { return ctx ? ctx->err : "no context"; }
+ZKB_EXPORT uint64_t zkb_kernel_launches(const zkb_ctx *ctx) { return ctx ? ctx->launches : 0; }
+ZKB_EXPORT uint64_t zkb_split_fixups(const zkb_ctx *ctx) { return ctx ? ctx->split_fixups : 0; }
+ZKB_EXPORT void *zkb_ctx_stream(zkb_ctx *ctx) { return ctx ? (void *)ctx->stream : NULL; }
+ZKB_EXPORT int zkb_ctx_sync(zkb_ctx *ctx)
+{
+	if (!ctx) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return ZKB_OK;
+}
+ZKB_EXPORT uint64_t zkb_decode_scratch_bytes(uint64_t nbytes, uint32_t nsessions)
+{
+	return zk_decode_scratch_need(nbytes, nsessions);
+}
+
+ZKB_EXPORT int zkb_decode_dev(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbytes,
+    const zkb_sessions *sess, const zkb_xidtab *xid, zkb_decoded *out)
+{
+	if (!ctx) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	return zk_decode_device(ctx, bytes, nbytes, sess, xid, out);
+}
+
+/* ---- carving columns out of one allocation ------------------------------------------ */
+
+struct Carver {
+	uint8_t *base;
+	size_t   off;
+	template <typename T> T *take(uint64_t n)
+	{
+		T *p = base ? reinterpret_cast<T *>(base + off) : NULL;
+		off += zk_align_up((size_t)n * sizeof (T) + 16, 256);
+		return p;
+	}
+};
+
+static size_t carve_decoded(zkb_decoded *d, uint8_t *base, uint64_t cf, uint64_t cs, uint64_t cb,
+    uint64_t ca, uint32_t nsess)
+{
+	Carver c = { base, 0 };
+	d->cap_frames = cf; d->cap_stat = cs; d->cap_buf = cb; d->cap_acl = ca;
+	d->frame_off = c.take<uint64_t>(cf); d->frame_len = c.take<int32_t>(cf);
+	d->session = c.take<uint32_t>(cf); d->meta = c.take<uint32_t>(cf);
+	d->xid = c.take<int32_t>(cf); d->zxid = c.take<int64_t>(cf); d->err = c.take<int32_t>(cf);
+	d->a0 = c.take<int32_t>(cf); d->a1 = c.take<int32_t>(cf);
+	d->stat_frame = c.take<uint32_t>(cs);
+	d->czxid = c.take<int64_t>(cs); d->mzxid = c.take<int64_t>(cs);
+	d->ctime = c.take<int64_t>(cs); d->mtime = c.take<int64_t>(cs);
+	d->version = c.take<int32_t>(cs); d->cversion = c.take<int32_t>(cs);
+	d->aversion = c.take<int32_t>(cs); d->ephemeralOwner = c.take<int64_t>(cs);
+	d->dataLength = c.take<int32_t>(cs); d->numChildren = c.take<int32_t>(cs);
+	d->pzxid = c.take<int64_t>(cs);
+	d->buf_frame = c.take<uint32_t>(cb); d->buf_off = c.take<uint64_t>(cb);
+	d->buf_len = c.take<int32_t>(cb);
+	d->acl_frame = c.take<uint32_t>(ca); d->acl_perms = c.take<int32_t>(ca);
+	d->sess_consumed = c.take<uint64_t>(nsess); d->sess_bad_length_at = c.take<uint64_t>(nsess);
+	d->sess_first_frame = c.take<uint32_t>((uint64_t)nsess + 1);
+	return c.off;
+}
+
+/* copy `n` rows of every column from a device-side layout to a host-side layout */
+static int copy_decoded_d2h(zkb_ctx *ctx, const zkb_decoded *dv, zkb_decoded *hv, uint32_t nsess)
+{
+#define CP(col, n)                                                                            \
+	if ((n) > 0)                                                                              \
+		ZK_CUDA(ctx, cudaMemcpyAsync(hv->col, dv->col, (size_t)(n) * sizeof (*hv->col),        \
+		    cudaMemcpyDeviceToHost, ctx->stream))
+	const uint64_t nf = dv->n_frames, ns = dv->n_stat, nb = dv->n_buf, na = dv->n_acl;
+	CP(frame_off, nf); CP(frame_len, nf); CP(session, nf); CP(meta, nf); CP(xid, nf); CP(zxid, nf);
+	CP(err, nf); CP(a0, nf); CP(a1, nf);
+	CP(stat_frame, ns); CP(czxid, ns); CP(mzxid, ns); CP(ctime, ns); CP(mtime, ns); CP(version, ns);
+	CP(cversion, ns); CP(aversion, ns); CP(ephemeralOwner, ns); CP(dataLength, ns);
+	CP(numChildren, ns); CP(pzxid, ns);
+	CP(buf_frame, nb); CP(buf_off, nb); CP(buf_len, nb);
+	CP(acl_frame, na); CP(acl_perms, na);
+	CP(sess_consumed, nsess); CP(sess_bad_length_at, nsess); CP(sess_first_frame, (uint64_t)nsess + 1);
+#undef CP
+	hv->n_frames = nf; hv->n_stat = ns; hv->n_buf = nb; hv->n_acl = na;
+	return ZKB_OK;
+}
+
+ZKB_EXPORT int zkb_decode_host(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbytes,
+    const zkb_sessions *sess, const zkb_xidtab *xid, zkb_decoded *out)
+{
+	int rc;
+	if (!ctx) return ZKB_EINVAL;
+	if (!sess || !sess->off || !out || (nbytes && !bytes)) {
+		snprintf(ctx->err, sizeof (ctx->err), "zkb_decode_host: NULL argument");
+		return ZKB_EINVAL;
+	}
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	const uint32_t nsess = sess->nsessions;
+	const bool have_xid = xid && xid->ops && xid->base && xid->count && xid->off;
+
+	/* ---- inputs: one device allocation, carved ---- */
+	Carver ci = { NULL, 0 };
+	ci.take<uint8_t>(nbytes + 32);
+	ci.take<uint64_t>((uint64_t)nsess + 1);
+	ci.take<uint8_t>(nsess); ci.take<uint32_t>(nsess);
+	ci.take<int32_t>(nsess); ci.take<uint32_t>(nsess); ci.take<uint64_t>(nsess);
+	ci.take<int8_t>(have_xid ? xid->nops : 0);
+	if ((rc = zk_ensure(ctx, &ctx->d_in, &ctx->d_in_bytes, ci.off, 0))) return rc;
+	ci.base = (uint8_t *)ctx->d_in; ci.off = 0;
+	uint8_t *d_bytes = ci.take<uint8_t>(nbytes + 32);
+	uint64_t *d_off = ci.take<uint64_t>((uint64_t)nsess + 1);
+	uint8_t *d_flags = ci.take<uint8_t>(nsess);
+	uint32_t *d_hs = ci.take<uint32_t>(nsess);
+	int32_t *d_xbase = ci.take<int32_t>(nsess);
+	uint32_t *d_xcount = ci.take<uint32_t>(nsess);
+	uint64_t *d_xoff = ci.take<uint64_t>(nsess);
+	int8_t *d_xops = ci.take<int8_t>(have_xid ? xid->nops : 0);
+
+#define H2D(dst, src, n)                                                                      \
+	if ((n) > 0)                                                                              \
+		ZK_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)(n), cudaMemcpyHostToDevice, ctx->stream))
+	H2D(d_bytes, bytes, nbytes);
+	H2D(d_off, sess->off, ((size_t)nsess + 1) * 8);
+	if (sess->flags) H2D(d_flags, sess->flags, nsess);
+	if (sess->handshake_frames) H2D(d_hs, sess->handshake_frames, (size_t)nsess * 4);
+	if (have_xid) {
+		H2D(d_xbase, xid->base, (size_t)nsess * 4);
+		H2D(d_xcount, xid->count, (size_t)nsess * 4);
+		H2D(d_xoff, xid->off, (size_t)nsess * 8);
+		H2D(d_xops, xid->ops, xid->nops);
+	}
+#undef H2D
+	zkb_sessions dsess;
+	dsess.nsessions = nsess; dsess.off = d_off;
+	dsess.flags = sess->flags ? d_flags : NULL;
+	dsess.handshake_frames = sess->handshake_frames ? d_hs : NULL;
+	zkb_xidtab dxid;
+	memset(&dxid, 0, sizeof (dxid));
+	if (have_xid) {
+		dxid.base = d_xbase; dxid.count = d_xcount; dxid.off = d_xoff; dxid.ops = d_xops;
+		dxid.nops = xid->nops;
+	}
+
+	/* ---- phase A gives the exact frame count, so FRAMES columns are sized exactly ---- */
+	uint64_t n_frames = 0;
+	if ((rc = zk_split_device(ctx, d_bytes, nbytes, &dsess, &n_frames))) return rc;
+
+	/* side tables: a Stat needs >= 88 input bytes, a buffer row >= 4; start from what typical
+	 * traffic needs and re-run phase B with the exact counts if that was too small */
+	uint64_t cs = n_frames < nbytes / 88 + 1 ? n_frames : nbytes / 88 + 1;
+	uint64_t cb = n_frames * 2 + nbytes / 64 + 16;
+	if (cb > nbytes / 4 + 1) cb = nbytes / 4 + 1;
+	uint64_t ca = n_frames / 2 + 16;
+	if (ca > nbytes / 12 + 1) ca = nbytes / 12 + 1;
+	zkb_decoded dv;
+	for (int attempt = 0;; ++attempt) {
+		memset(&dv, 0, sizeof (dv));
+		size_t need = carve_decoded(&dv, NULL, n_frames, cs, cb, ca, nsess);
+		if ((rc = zk_ensure(ctx, &ctx->d_out, &ctx->d_out_bytes, need, 0))) return rc;
+		carve_decoded(&dv, (uint8_t *)ctx->d_out, n_frames, cs, cb, ca, nsess);
+		rc = zk_fields_device(ctx, d_bytes, nbytes, &dsess, have_xid ? &dxid : NULL, n_frames, &dv);
+		if (rc == ZKB_EOVERFLOW && attempt == 0) {
+			cs = dv.n_stat; cb = dv.n_buf; ca = dv.n_acl;
+			continue;
+		}
+		if (rc) return rc;
+		break;
+	}
+
+	/* ---- results: exact-size pinned host columns ---- */
+	zkb_decoded hv;
+	memset(&hv, 0, sizeof (hv));
+	size_t hneed = carve_decoded(&hv, NULL, dv.n_frames, dv.n_stat, dv.n_buf, dv.n_acl, nsess);
+	if ((rc = zk_ensure(ctx, &ctx->h_out, &ctx->h_out_bytes, hneed, 1))) return rc;
+	carve_decoded(&hv, (uint8_t *)ctx->h_out, dv.n_frames, dv.n_stat, dv.n_buf, dv.n_acl, nsess);
+	if ((rc = copy_decoded_d2h(ctx, &dv, &hv, nsess))) return rc;
+	ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	*out = hv;
+	return ZKB_OK;
+}
+
+/* ---- xid table ------------------------------------------------------------------------ */
+
+ZKB_EXPORT int zkb_xidtab_build_dev(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessions,
+    const zkb_xidtab *layout, int8_t *ops_out)
+{
+	if (!ctx) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	return zk_xidtab_build_device(ctx, req, nsessions, layout, ops_out);
+}
+
+ZKB_EXPORT int zkb_xidtab_build_host(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessions,
+    const zkb_xidtab *layout, int8_t *ops_out)
+{
+	int rc;
+	if (!ctx) return ZKB_EINVAL;
+	if (!req || !layout || !ops_out) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	const uint64_t nf = req->n_frames, nops = layout->nops;
+	Carver ci = { NULL, 0 };
+	ci.take<uint32_t>(nf); ci.take<int32_t>(nf); ci.take<uint32_t>(nf); ci.take<int32_t>(nf);
+	ci.take<int32_t>(nsessions); ci.take<uint32_t>(nsessions); ci.take<uint64_t>(nsessions);
+	ci.take<int8_t>(nops);
+	if ((rc = zk_ensure(ctx, &ctx->d_in, &ctx->d_in_bytes, ci.off, 0))) return rc;
+	ci.base = (uint8_t *)ctx->d_in; ci.off = 0;
+	zkb_decoded dreq;
+	memset(&dreq, 0, sizeof (dreq));
+	dreq.n_frames = nf;
+	dreq.meta = ci.take<uint32_t>(nf); dreq.frame_len = ci.take<int32_t>(nf);
+	dreq.session = ci.take<uint32_t>(nf); dreq.xid = ci.take<int32_t>(nf);
+	int32_t *d_base = ci.take<int32_t>(nsessions);
+	uint32_t *d_count = ci.take<uint32_t>(nsessions);
+	uint64_t *d_off = ci.take<uint64_t>(nsessions);
+	int8_t *d_ops = ci.take<int8_t>(nops);
+#define H2D(dst, src, n)                                                                      \
+	if ((n) > 0)                                                                              \
+		ZK_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)(n), cudaMemcpyHostToDevice, ctx->stream))
+	H2D(dreq.meta, req->meta, nf * 4); H2D(dreq.frame_len, req->frame_len, nf * 4);
+	H2D(dreq.session, req->session, nf * 4); H2D(dreq.xid, req->xid, nf * 4);
+	H2D(d_base, layout->base, (size_t)nsessions * 4);
+	H2D(d_count, layout->count, (size_t)nsessions * 4);
+	H2D(d_off, layout->off, (size_t)nsessions * 8);
+#undef H2D
+	zkb_xidtab dl;
+	memset(&dl, 0, sizeof (dl));
+	dl.base = d_base; dl.count = d_count; dl.off = d_off; dl.nops = nops;
+	if ((rc = zk_xidtab_build_device(ctx, &dreq, nsessions, &dl, d_ops))) return rc;
+	if (nops)
+		ZK_CUDA(ctx, cudaMemcpyAsync(ops_out, d_ops, nops, cudaMemcpyDeviceToHost, ctx->stream));
+	ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return ZKB_OK;
+}
+
+/* ---- encode ----------------------------------------------------------------------------- */
+
+ZKB_EXPORT int zkb_encode_dev(zkb_ctx *ctx, const zkb_requests *req, uint8_t *out, uint64_t out_cap,
+    uint64_t *frame_off, uint8_t *status, uint64_t *out_len)
+{
+	if (!ctx) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	return zk_encode_device(ctx, req, out, out_cap, frame_off, status, out_len);
+}
+
+ZKB_EXPORT int zkb_encode_host(zkb_ctx *ctx, const zkb_requests *req, const uint8_t **out,
+    const uint64_t **frame_off, const uint8_t **status, uint64_t *out_len)
+{
+	int rc;
+	if (!ctx) return ZKB_EINVAL;
+	if (!req || !out || !frame_off || !status || !out_len) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	const uint64_t n = req->n, ne = req->n_elem, na = req->n_acl, al = req->arena_len;
+	Carver ci = { NULL, 0 };
+	zkb_requests d;
+	memset(&d, 0, sizeof (d));
+	/* size pass then carve pass */
+	for (int pass = 0; pass < 2; ++pass) {
+		ci.off = 0;
+		d.xid = ci.take<int32_t>(n); d.op = ci.take<int8_t>(n);
+		d.arena = ci.take<uint8_t>(al);
+		d.path_off = ci.take<uint64_t>(n); d.path_len = ci.take<int32_t>(n);
+		d.data_off = ci.take<uint64_t>(n); d.data_len = ci.take<int32_t>(n);
+		d.a0 = ci.take<int32_t>(n); d.a1 = ci.take<int32_t>(n);
+		d.zxid = ci.take<int64_t>(n); d.zxid2 = ci.take<int64_t>(n);
+		d.vec_first = ci.take<uint32_t>(n); d.vec_count = ci.take<int32_t>(n);
+		d.n0 = ci.take<int32_t>(n); d.n1 = ci.take<int32_t>(n);
+		d.elem_off = ci.take<uint64_t>(ne); d.elem_len = ci.take<int32_t>(ne);
+		d.acl_perms = ci.take<int32_t>(na);
+		d.acl_scheme_off = ci.take<uint64_t>(na); d.acl_scheme_len = ci.take<int32_t>(na);
+		d.acl_id_off = ci.take<uint64_t>(na); d.acl_id_len = ci.take<int32_t>(na);
+		if (pass == 0) {
+			if ((rc = zk_ensure(ctx, &ctx->d_in, &ctx->d_in_bytes, ci.off, 0))) return rc;
+			ci.base = (uint8_t *)ctx->d_in;
+		}
+	}
+	d.n = n; d.arena_len = al; d.n_elem = ne; d.n_acl = na;
+#define H2D(field, cnt)                                                                       \
+	if ((cnt) > 0 && req->field)                                                              \
+		ZK_CUDA(ctx, cudaMemcpyAsync((void *)d.field, req->field, (size_t)(cnt) * sizeof (*req->field), \
+		    cudaMemcpyHostToDevice, ctx->stream))
+	H2D(xid, n); H2D(op, n); H2D(arena, al); H2D(path_off, n); H2D(path_len, n); H2D(data_off, n);
+	H2D(data_len, n); H2D(a0, n); H2D(a1, n); H2D(zxid, n); H2D(zxid2, n); H2D(vec_first, n);
+	H2D(vec_count, n); H2D(n0, n); H2D(n1, n); H2D(elem_off, ne); H2D(elem_len, ne);
+	H2D(acl_perms, na); H2D(acl_scheme_off, na); H2D(acl_scheme_len, na); H2D(acl_id_off, na);
+	H2D(acl_id_len, na);
+#undef H2D
+	/* outputs: frame_off[n+1], status[n], then the bytes once their total is known */
+	Carver co = { NULL, 0 };
+	co.take<uint64_t>(n + 1); co.take<uint8_t>(n);
+	size_t fixed = co.off;
+	if ((rc = zk_ensure(ctx, &ctx->d_out, &ctx->d_out_bytes, fixed + 256, 0))) return rc;
+	co.base = (uint8_t *)ctx->d_out; co.off = 0;
+	uint64_t *d_fo = co.take<uint64_t>(n + 1);
+	uint8_t *d_st = co.take<uint8_t>(n);
+	uint64_t total = 0;
+	uint64_t cap = ctx->d_out_bytes - fixed;
+	uint8_t *d_bytes = (uint8_t *)ctx->d_out + fixed;
+	rc = zk_encode_device(ctx, &d, d_bytes, cap, d_fo, d_st, &total);
+	if (rc == ZKB_EOVERFLOW) {
+		/* growing d_out moves it: redo the whole encode into the larger buffer */
+		if ((rc = zk_ensure(ctx, &ctx->d_out, &ctx->d_out_bytes, fixed + total + 256, 0))) return rc;
+		co.base = (uint8_t *)ctx->d_out; co.off = 0;
+		d_fo = co.take<uint64_t>(n + 1);
+		d_st = co.take<uint8_t>(n);
+		d_bytes = (uint8_t *)ctx->d_out + fixed;
+		cap = ctx->d_out_bytes - fixed;
+		rc = zk_encode_device(ctx, &d, d_bytes, cap, d_fo, d_st, &total);
+	}
+	if (rc) return rc;
+	Carver ch = { NULL, 0 };
+	ch.take<uint64_t>(n + 1); ch.take<uint8_t>(n); ch.take<uint8_t>(total);
+	if ((rc = zk_ensure(ctx, &ctx->h_out, &ctx->h_out_bytes, ch.off, 1))) return rc;
+	ch.base = (uint8_t *)ctx->h_out; ch.off = 0;
+	uint64_t *h_fo = ch.take<uint64_t>(n + 1);
+	uint8_t *h_st = ch.take<uint8_t>(n);
+	uint8_t *h_bytes = ch.take<uint8_t>(total);
+	ZK_CUDA(ctx, cudaMemcpyAsync(h_fo, d_fo, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	if (n) ZK_CUDA(ctx, cudaMemcpyAsync(h_st, d_st, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+	if (total) ZK_CUDA(ctx, cudaMemcpyAsync(h_bytes, d_bytes, (size_t)total, cudaMemcpyDeviceToHost, ctx->stream));
+	ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	*out = h_bytes; *frame_off = h_fo; *status = h_st; *out_len = total;
+	return ZKB_OK;
+}

@@ -1,0 +1,94 @@
+/*
+ * zk_internal.h — shared between the translation units of libzkbatch.so.
+ * Not part of the public ABI (that is include/zkbatch.h).
+ */
+#ifndef ZK_INTERNAL_H
+#define ZK_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/zkbatch.h"
+
+/* ---- geometry ---------------------------------------------------------------------- */
+#define ZK_TILE_BYTES     32768u  /* bytes of input one decode CTA stages in shared memory */
+#define ZK_TILE_OVERHANG   2048u  /* extra bytes staged so frames that start near the end of a
+                                     tile are still read from shared memory */
+#define ZK_DECODE_THREADS   256
+#define ZK_GRAN_MIN_LOG2     10   /* splitter granule: 1 KiB .. 32 KiB (<= tile) */
+#define ZK_GRAN_MAX_LOG2     15
+#define ZK_MAX_BATCH_BYTES ((1ull << 34) - 1)  /* keeps every row index below 2^32 */
+
+#define ZK_NONE     0xFFFFFFFFFFFFFFFFull  /* no live chain */
+#define ZK_INHERIT  0xFFFFFFFFFFFFFFFEull  /* granule did not touch the chain */
+
+/* look-back flags */
+#define ZK_LB_EMPTY 0u
+#define ZK_LB_AGG   1u
+#define ZK_LB_PFX   2u
+
+/* device error bits (d_ctrl->error) */
+#define ZK_DERR_SESSIONS  1u  /* session offsets not monotone / not covering the batch */
+#define ZK_DERR_LOOKBACK  2u  /* look-back spin limit hit (would have been a hang) */
+#define ZK_DERR_COUNT     4u  /* frame count disagreed between split and emit */
+
+struct zk_ctrl {
+	unsigned int       error;
+	unsigned int       n_dirty;
+	unsigned int       ticket;
+	unsigned int       pad0;
+	unsigned long long n_frames;
+	unsigned long long n_stat, n_buf, n_acl;
+	unsigned long long enc_bytes;
+};
+
+struct zkb_ctx {
+	int           device;
+	cudaStream_t  stream;
+	char          err[512];
+	uint64_t      launches;
+	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
+	/* device scratch (grown on demand, never shrunk) */
+	void         *d_scratch;   size_t d_scratch_bytes;
+	zk_ctrl      *d_ctrl;
+	zk_ctrl      *h_ctrl;      /* pinned */
+	/* host-variant staging */
+	void         *d_in;        size_t d_in_bytes;      /* batch bytes + session arrays + xid table */
+	void         *d_out;       size_t d_out_bytes;     /* every output column */
+	void         *h_out;       size_t h_out_bytes;     /* pinned mirror of d_out */
+	void         *h_in;        size_t h_in_bytes;      /* pinned bounce buffer for small arrays */
+	int           sm_count;
+};
+
+#define ZK_CUDA(ctx, call)                                                              \
+	do {                                                                                \
+		cudaError_t e__ = (call);                                                       \
+		if (e__ != cudaSuccess) {                                                       \
+			snprintf((ctx)->err, sizeof ((ctx)->err), "%s:%d: %s: %s", __FILE__, __LINE__, \
+			    #call, cudaGetErrorString(e__));                                        \
+			return ZKB_ECUDA;                                                           \
+		}                                                                               \
+	} while (0)
+
+static inline size_t zk_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int zk_ensure(zkb_ctx *ctx, void **p, size_t *have, size_t need, int pinned_host);
+
+/* decode pipeline on device pointers; defined in zk_decode.cu */
+int zk_decode_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
+    const zkb_sessions *d_sess, const zkb_xidtab *d_xid, zkb_decoded *d_out);
+int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
+    const zkb_sessions *d_sess, uint64_t *n_frames);
+int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
+    const zkb_sessions *d_sess, const zkb_xidtab *d_xid, uint64_t n_frames, zkb_decoded *d_out);
+int zk_xidtab_build_device(zkb_ctx *ctx, const zkb_decoded *d_req, uint32_t nsessions,
+    const zkb_xidtab *d_layout, int8_t *d_ops_out);
+/* encode pipeline on device pointers; defined in zk_encode.cu */
+int zk_encode_device(zkb_ctx *ctx, const zkb_requests *d_req, uint8_t *d_out, uint64_t out_cap,
+    uint64_t *d_frame_off, uint8_t *d_status, uint64_t *out_len);
+size_t zk_decode_scratch_need(uint64_t nbytes, uint32_t nsessions);
+size_t zk_encode_scratch_need(uint64_t n);
+
+#endif

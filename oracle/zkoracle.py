@@ -1,0 +1,118 @@
+"""TEST INFRASTRUCTURE — ctypes binding of oracle/libzkoracle.so (oracle/zkoracle.c).
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this.
+It reuses the product's ctypes struct mirrors (the oracle emits the same columnar layout
+so results compare with array equality) but shares no codec code with the product.
+"""
+import ctypes as C
+import importlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+zk = importlib.import_module("node-zkstream_b200")
+_abi = zk._abi
+Columns = zk.Columns
+
+LIB = os.path.join(HERE, "libzkoracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(HERE, "zkoracle.c")
+    hdr = os.path.join(ROOT, "include", "zkbatch.h")
+    if (force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(src)
+            or os.path.getmtime(LIB) < os.path.getmtime(hdr)):
+        subprocess.run(["gcc", "-O2", "-Wall", "-fPIC", "-shared", "-o", LIB, src, "-lpthread"], check=True)
+    return LIB
+
+
+def load():
+    global _lib
+    if _lib is None:
+        build()
+        lib = C.CDLL(LIB)
+        P = C.c_void_p
+        lib.zko_decode.restype = C.c_int
+        lib.zko_decode.argtypes = [P, C.c_uint64, C.POINTER(_abi.Sessions), C.POINTER(_abi.XidTab), C.c_int,
+                                   C.c_uint64, C.POINTER(_abi.Decoded), C.POINTER(P)]
+        lib.zko_free.argtypes = [P]
+        lib.zko_bench_decode.restype = C.c_double
+        lib.zko_bench_decode.argtypes = [P, C.c_uint64, C.POINTER(_abi.Sessions), C.POINTER(_abi.XidTab),
+                                         C.c_int, C.c_uint64, C.c_int, C.POINTER(C.c_uint64),
+                                         C.POINTER(C.c_uint64)]
+        lib.zko_xidtab_build.restype = C.c_int
+        lib.zko_xidtab_build.argtypes = [C.POINTER(_abi.Decoded), C.c_uint32, C.POINTER(_abi.XidTab), P]
+        lib.zko_encode.restype = C.c_int
+        lib.zko_encode.argtypes = [C.POINTER(_abi.Requests), C.POINTER(P), C.POINTER(C.c_uint64), P, P]
+        lib.zko_buf_free.argtypes = [P]
+        _lib = lib
+    return _lib
+
+
+def _sessions(nbytes, sess_off, flags, hs):
+    return zk.Context._sessions(nbytes, sess_off, flags, hs)
+
+
+def decode(data, sess_off=None, flags=None, handshake_frames=None, xidtab=None, mode=0, chunk=65536):
+    """CPU decode of a batch.  mode 0 = in place, 1 = faithful (chunked, copy + memmove per frame)."""
+    lib = load()
+    buf = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data)
+    s, keep = _sessions(buf.size, sess_off, flags, handshake_frames)
+    xt = xidtab.struct() if xidtab is not None else None
+    out = _abi.Decoded()
+    h = C.c_void_p()
+    rc = lib.zko_decode(buf.ctypes.data if buf.size else None, buf.size, C.byref(s),
+                        C.byref(xt) if xt is not None else None, mode, chunk, C.byref(out), C.byref(h))
+    if rc != 0:
+        raise ValueError("zko_decode failed: %d" % rc)
+    cols = Columns.from_struct(out, s.nsessions, copy=True)
+    lib.zko_free(h)
+    del keep
+    return cols
+
+
+def bench_decode(data, sess_off, flags, handshake_frames, xidtab, mode, chunk, nthreads):
+    """Timed multi-thread CPU decode; returns (seconds, frames)."""
+    lib = load()
+    buf = np.ascontiguousarray(data, dtype=np.uint8)
+    s, keep = _sessions(buf.size, sess_off, flags, handshake_frames)
+    xt = xidtab.struct() if xidtab is not None else None
+    frames, chk = C.c_uint64(), C.c_uint64()
+    sec = lib.zko_bench_decode(buf.ctypes.data, buf.size, C.byref(s), C.byref(xt) if xt is not None else None,
+                               mode, chunk, nthreads, C.byref(frames), C.byref(chk))
+    del keep
+    return sec, frames.value
+
+
+def xidtab_build(req_cols, layout):
+    lib = load()
+    d = _abi.Decoded()
+    d.n_frames = req_cols.n_frames
+    d.meta, d.frame_len = req_cols.meta.ctypes.data, req_cols.frame_len.ctypes.data
+    d.session, d.xid = req_cols.session.ctypes.data, req_cols.xid.ctypes.data
+    t = layout.struct()
+    ops = np.empty(layout.nops, dtype=np.int8)
+    lib.zko_xidtab_build(C.byref(d), len(layout.count), C.byref(t), ops.ctypes.data if ops.size else None)
+    return zk.XidTable(layout.base, layout.count, ops)
+
+
+def encode(req):
+    """req: RequestBatch.  Returns (bytes ndarray, frame_off, status) like Context.encode_host."""
+    lib = load()
+    r, keep = req.struct()
+    out = C.c_void_p()
+    n = C.c_uint64()
+    fo = np.zeros(req.n + 1, dtype=np.uint64)
+    st = np.zeros(max(req.n, 1), dtype=np.uint8)
+    lib.zko_encode(C.byref(r), C.byref(out), C.byref(n), fo.ctypes.data, st.ctypes.data)
+    data = np.ctypeslib.as_array(C.cast(out, C.POINTER(C.c_uint8)), shape=(n.value,)).copy() if n.value else np.zeros(0, np.uint8)
+    lib.zko_buf_free(out)
+    del keep
+    return data, fo, st[:req.n]

@@ -1,0 +1,136 @@
+"""GPU parity: libzkbatch.so (through its C ABI, host-buffer entry point) against the CPU
+oracle on the same seeded bytes — every column bit-exact."""
+import base64
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CAPTURE1 = [  # reference test/streams.test.js:21-27
+    ("send", "AAAALQAAAAAAAAAAAAAAAAAAdTAAAAAAAAAAAAAAABAAAAAAAAAAAAAAAAAAAAAAAA=="),
+    ("recv", "AAAAJQAAAAAAAHUwAVWjqFbbAAAAAAAQh19uvwgo25o9B6hUkSvqKQA="),
+    ("send", "AAAADgAAAAEAAAAIAAAAAS8A"),
+    ("recv", "AAAAKAAAAAEAAAAAAAAFFwAAAAAAAAACAAAACXpvb2tlZXBlcgAAAANmb28="),
+]
+
+
+def both(ctx, oracle, corpus, xt="auto"):
+    d, off, fl, hs = corpus.arrays()
+    if xt == "auto":
+        xt = corpus.xidtable()
+    g = ctx.decode_host(d, off, fl, hs, xt)
+    o = oracle.decode(d, off, fl, hs, xt)
+    return g, o
+
+
+def test_capture1(ctx, oracle, synth):
+    b = [base64.b64decode(x) for _, x in CAPTURE1]
+    c = synth.Corpus()
+    c.add(b[0] + b[2], server=True)
+    c.add(b[1] + b[3], xidmap={1: 8})
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+    assert g.n_frames == 4 and g.n_buf == 5
+    assert g.a0[3] == 2 and g.zxid[3] == 0x517
+    assert bytes(c.data[int(g.buf_off[3]):int(g.buf_off[3]) + int(g.buf_len[3])]) == b"zookeeper"
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_fuzz(ctx, oracle, synth, seed):
+    g, o = both(ctx, oracle, synth.fuzz_corpus(seed))
+    assert g.diff(o) == []
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_fuzz_big(ctx, oracle, synth, seed):
+    g, o = both(ctx, oracle, synth.fuzz_corpus(1000 + seed, nsessions=400, max_frames=300))
+    assert g.diff(o) == []
+    assert g.n_frames > 1000
+
+
+def test_cfg1_getdata(ctx, oracle, synth):
+    g, o = both(ctx, oracle, synth.cfg1_getdata(20000))
+    assert g.diff(o) == []
+    assert g.n_frames == 20001 and g.n_stat == 20000 and g.n_buf == 20001
+    assert (g.status == 0).all()
+
+
+def test_cfg2_mixed(ctx, oracle, synth):
+    g, o = both(ctx, oracle, synth.cfg2_mixed(16, 1500))
+    assert g.diff(o) == []
+
+
+def test_cfg2_xidtab_from_requests(ctx, oracle, synth, zk):
+    """Build the response side's xid table from the decoded request side (zk-streams.js:145)."""
+    c = synth.cfg2_mixed(8, 400, seed=9)
+    n = 8
+    d, off, fl, hs = c.arrays()
+    req = ctx.decode_host(d[: int(off[n])], off[: n + 1], fl[:n], hs[:n], None)
+    layout = zk.XidTable(np.zeros(n, np.int32), np.full(n, 400, np.uint32))
+    xt_g = ctx.xidtab_build_host(req, layout)
+    xt_o = oracle.xidtab_build(oracle.decode(d[: int(off[n])], off[: n + 1], fl[:n], hs[:n], None), layout)
+    assert np.array_equal(xt_g.ops, xt_o.ops)
+    rsp = d[int(off[n]):]
+    roff = off[n:] - off[n]
+    g = ctx.decode_host(rsp, roff, fl[n:], hs[n:], xt_g)
+    o = oracle.decode(rsp, roff, fl[n:], hs[n:], xt_o)
+    assert g.diff(o) == []
+    # every reply that names a request decodes (PING replies use the special xid)
+    assert (g.status == 0).all()
+
+
+def test_cfg3_tiny(ctx, oracle, synth):
+    g, o = both(ctx, oracle, synth.cfg3_tiny(50, 800))
+    assert g.diff(o) == []
+
+
+def test_cfg4_large(ctx, oracle, synth):
+    g, o = both(ctx, oracle, synth.cfg4_large(6, payload=300000, children=(3000, 9000)))
+    assert g.diff(o) == []
+
+
+def test_empty_and_ragged(ctx, oracle, synth):
+    c = synth.Corpus()
+    g, o = both(ctx, oracle, c, xt=None)          # zero sessions, zero bytes
+    assert g.diff(o) == [] and g.n_frames == 0
+    c = synth.Corpus()
+    c.add(b""); c.add(b""); c.add(b"\x00"); c.add(b""); c.add(b"\x00\x00\x00"); c.add(b"")
+    g, o = both(ctx, oracle, c, xt=None)
+    assert g.diff(o) == [] and g.n_frames == 0
+    assert list(g.sess_consumed) == [0, 0, 0, 1, 1, 4]
+
+
+def test_bad_lengths(ctx, oracle, synth):
+    """reference test/nasty.test.js:125-126,148,170"""
+    c = synth.Corpus()
+    c.add(bytes.fromhex("40004000"))
+    c.add(bytes.fromhex("000000000102"))
+    c.add(bytes.fromhex("fffffffe0102"))
+    c.add(bytes.fromhex("01000000") + bytes(16))          # exactly 16 MiB: legal, incomplete
+    c.add(bytes.fromhex("01000001") + bytes(16))          # 16 MiB + 1: BAD_LENGTH
+    g, o = both(ctx, oracle, c, xt=None)
+    assert g.diff(o) == []
+    NO = 0xFFFFFFFFFFFFFFFF
+    assert list(g.sess_bad_length_at) == [0, NO, 10, NO, 36]
+    assert g.n_frames == 1 and g.status[0] == 1          # zero-length frame: BAD_DECODE
+
+
+def test_adversarial_split(ctx, oracle, synth):
+    """Payloads that look like frame headers at every offset must not fool the splitter."""
+    import random
+    rng = random.Random(5)
+    fake = synth.frame(synth.resp_header(7, 9, 0) + synth.stat_bytes(rng))
+    parts = [synth.frame(synth.connect_response(rng))]
+    xm = {}
+    for i in range(3000):
+        data = (fake * rng.randrange(1, 40))[rng.randrange(0, 5):]
+        parts.append(synth.frame(synth.resp_header(i, i, 0) + synth.jbuf(data) + synth.stat_bytes(rng)))
+        xm[i] = 4
+    c = synth.Corpus()
+    c.add(b"".join(parts), xidmap=xm)
+    before = ctx.split_fixups
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+    assert g.n_frames == 3001
+    print("split fixups used:", ctx.split_fixups - before)
