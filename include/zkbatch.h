@@ -282,6 +282,15 @@ uint64_t zkb_kernel_launches(const zkb_ctx *ctx);
 /* Number of extra splitter iterations (entry-point guesses that had to be corrected) this
  * context has needed so far; 0 on ordinary traffic.  Diagnostic only. */
 uint64_t zkb_split_fixups(const zkb_ctx *ctx);
+/* Frames of the last decode call that were not well-formed (or reached past the staged
+ * tile) and therefore went through the exact, slower reader.  Diagnostic only. */
+uint64_t zkb_last_slow_frames(const zkb_ctx *ctx);
+/* Per-phase device timing of decode calls.  With timing on, each zkb_decode_* records CUDA
+ * events on the context's stream around its three phases; zkb_last_phase_ms returns the
+ * milliseconds the last call spent in { frame split (first pass), frame-row emit, field
+ * decode kernel }.  Off by default. */
+int zkb_ctx_set_timing(zkb_ctx *ctx, int on);
+int zkb_last_phase_ms(const zkb_ctx *ctx, float out[3]);
 /* The cudaStream_t the context launches on, as an opaque pointer (for event timing). */
 void *zkb_ctx_stream(zkb_ctx *ctx);
 int  zkb_ctx_sync(zkb_ctx *ctx);

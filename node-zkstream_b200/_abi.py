@@ -71,6 +71,9 @@ SYMBOLS = [
     ("zkb_last_error", C.c_char_p, [P]),
     ("zkb_kernel_launches", C.c_uint64, [P]),
     ("zkb_split_fixups", C.c_uint64, [P]),
+    ("zkb_last_slow_frames", C.c_uint64, [P]),
+    ("zkb_ctx_set_timing", C.c_int, [P, C.c_int]),
+    ("zkb_last_phase_ms", C.c_int, [P, C.POINTER(C.c_float * 3)]),
     ("zkb_ctx_stream", P, [P]),
     ("zkb_ctx_sync", C.c_int, [P]),
     ("zkb_decode_scratch_bytes", C.c_uint64, [C.c_uint64, C.c_uint32]),

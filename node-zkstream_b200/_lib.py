@@ -127,8 +127,21 @@ class Context:
         return int(self._lib.zkb_split_fixups(self._h))
 
     @property
+    def last_slow_frames(self):
+        return int(self._lib.zkb_last_slow_frames(self._h))
+
+    @property
     def stream(self):
         return self._lib.zkb_ctx_stream(self._h)
+
+    def set_timing(self, on=True):
+        self._check(self._lib.zkb_ctx_set_timing(self._h, 1 if on else 0))
+
+    def last_phase_ms(self):
+        """(split, emit, decode) device milliseconds of the last decode call (timing must be on)."""
+        out = (C.c_float * 3)()
+        self._check(self._lib.zkb_last_phase_ms(self._h, C.byref(out)))
+        return tuple(float(x) for x in out)
 
     def sync(self):
         self._check(self._lib.zkb_ctx_sync(self._h))

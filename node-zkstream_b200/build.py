@@ -31,7 +31,19 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+GEN_LIB = os.path.join(HERE, "libzkgen.so")
+
+
+def build_gen(force=False):
+    """libzkgen.so: the host-side synthetic traffic generator (plain C, no codec in it)."""
+    src = os.path.join(CSRC, "zkgen.c")
+    if force or not os.path.exists(GEN_LIB) or os.path.getmtime(GEN_LIB) < os.path.getmtime(src):
+        subprocess.run(["gcc", "-O2", "-Wall", "-fPIC", "-shared", "-o", GEN_LIB, src, "-lpthread"], check=True)
+    return GEN_LIB
+
+
 def build(force=False, verbose=False):
+    build_gen(force)
     if not force and not _stale():
         return LIB
     objs = []

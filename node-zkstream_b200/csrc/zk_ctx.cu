@@ -81,12 +81,29 @@ ZKB_EXPORT void zkb_ctx_destroy(zkb_ctx *ctx)
 	if (ctx->d_out) cudaFree(ctx->d_out);
 	if (ctx->h_out) cudaFreeHost(ctx->h_out);
 	if (ctx->h_in) cudaFreeHost(ctx->h_in);
+	for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
 	delete ctx;
 }
 
 ZKB_EXPORT const char *zkb_last_error(const zkb_ctx *ctx) { return ctx ? ctx->err : "no context"; }
 ZKB_EXPORT uint64_t zkb_kernel_launches(const zkb_ctx *ctx) { return ctx ? ctx->launches : 0; }
 ZKB_EXPORT uint64_t zkb_split_fixups(const zkb_ctx *ctx) { return ctx ? ctx->split_fixups : 0; }
+ZKB_EXPORT uint64_t zkb_last_slow_frames(const zkb_ctx *ctx) { return ctx ? ctx->slow_frames : 0; }
+ZKB_EXPORT int zkb_ctx_set_timing(zkb_ctx *ctx, int on)
+{
+	if (!ctx) return ZKB_EINVAL;
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	if (on && !ctx->ev[0])
+		for (int i = 0; i < 6; i++) ZK_CUDA(ctx, cudaEventCreate(&ctx->ev[i]));
+	ctx->timing = on ? 1 : 0;
+	return ZKB_OK;
+}
+ZKB_EXPORT int zkb_last_phase_ms(const zkb_ctx *ctx, float out[3])
+{
+	if (!ctx || !out) return ZKB_EINVAL;
+	out[0] = ctx->phase_ms[0]; out[1] = ctx->phase_ms[1]; out[2] = ctx->phase_ms[2];
+	return ZKB_OK;
+}
 ZKB_EXPORT void *zkb_ctx_stream(zkb_ctx *ctx) { return ctx ? (void *)ctx->stream : NULL; }
 ZKB_EXPORT int zkb_ctx_sync(zkb_ctx *ctx)
 {

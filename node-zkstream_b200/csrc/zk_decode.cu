@@ -66,15 +66,19 @@ __device__ __forceinline__ uint4 ld_stream16(const uint4 *p)
 	return r;
 }
 
-__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
+/* look-back descriptors: one 128-bit relaxed gpu-scope access each way (never cached in
+ * L1, never hoisted out of the polling loop) */
+__device__ __forceinline__ uint4 ld_desc(const uint4 *p)
 {
-	uint32_t v;
-	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-	return v;
+	uint4 r;
+	asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+	    : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+	return r;
 }
-__device__ __forceinline__ void st_release(uint32_t *p, uint32_t v)
+__device__ __forceinline__ void st_desc(uint4 *p, uint4 v)
 {
-	asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+	asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};"
+	    :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 /* ================================================================================== */
@@ -90,12 +94,17 @@ struct SplitArgs {
 	const uint8_t  *sess_flags;
 	uint32_t        glog2;
 	uint32_t        n_gran;
-	uint64_t       *g_assumed;   /* entry position the last walk of the granule assumed */
+	/* two walk results per granule ([version * n_gran + g]): version 0 is the walk from the
+	 * granule's own guess, version 1 the latest walk from a carried position; g_sel says
+	 * which one the scan uses */
+	uint64_t       *g_assumed;   /* entry position the walk assumed */
 	uint64_t       *g_out;       /* exit: next frame start >= granule end | NONE | INHERIT */
-	uint64_t       *g_carry;     /* scan result: exit of the nearest predecessor that had one */
 	uint32_t       *g_cnt;       /* frames starting in the granule */
+	uint8_t        *g_sel;
+	uint64_t       *g_carry;     /* scan result: exit of the nearest predecessor that had one */
 	uint32_t       *g_base;      /* exclusive prefix of g_cnt */
 	uint8_t        *g_dirty;
+	uint32_t       *g_src;       /* 1 + index of the granule whose exit is this granule's carry; 0 = none */
 	/* EMIT */
 	uint64_t       *frame_off;
 	int32_t        *frame_len;
@@ -119,36 +128,147 @@ __device__ __forceinline__ uint32_t lower_bound_u64(const uint64_t *off, uint32_
 }
 
 /* Does a frame header that makes sense for this direction start at p?  Ranking only:
- * a wrong answer costs a FIX iteration, never a wrong result. */
+ * a wrong answer costs a FIX iteration, never a wrong result.  Both words are loaded
+ * before either is tested so the two misses overlap. */
 __device__ bool header_plausible(const uint8_t *bytes, uint64_t p, uint64_t send, bool server,
     uint64_t &next)
 {
-	if (p + 4 > send) return false;
-	uint32_t b0 = __ldg(bytes + p);
-	if (b0 > 1) return false;                       /* len <= 16 MiB => first byte 0 or 1 */
-	int32_t len = (int32_t)g_be32(bytes, p);
-	if (!len_ok(len)) return false;
+	const uint32_t fld = server ? 8u : 16u;      /* type (requests) / err (responses) */
+	if (p + 4 + fld + 4 > send) return false;
+	const int32_t len = (int32_t)g_be32(bytes, p);
+	const int32_t f = (int32_t)g_be32(bytes, p + 4 + fld - 4);
+	if (len < (int32_t)fld || len > ZKB_MAX_PACKET) return false;
 	if (p + 4 + (uint64_t)len > send) return false;
-	if (server) {
-		if (len < 8) return false;
-		if (!op_known((int32_t)g_be32(bytes, p + 8))) return false;
-	} else {
-		if (len < 16) return false;
-		if (!err_known((int32_t)g_be32(bytes, p + 16))) return false;
-	}
+	if (server ? !op_known(f) : !err_known(f)) return false;
 	next = p + 4 + (uint64_t)len;
 	return true;
 }
 
+/* Follow the chain `hops` more frames from q: a false start almost never survives this,
+ * a true one always does (a legitimately incomplete or final frame ends the check). */
+__device__ bool chain_plausible(const uint8_t *bytes, uint64_t q, uint64_t send, bool server, int hops)
+{
+	for (int k = 0; k < hops; ++k) {
+		if (q == send || q + 4 > send) return true;
+		uint64_t n2;
+		if (!header_plausible(bytes, q, send, server, n2)) {
+			/* the chain may end in a frame that is not complete yet, but only one whose
+			 * header is sane: a wild length that overruns the session proves nothing */
+			const uint32_t fld = server ? 8u : 16u;
+			if (q + 8 + fld > send) return true;
+			const int32_t l = (int32_t)g_be32(bytes, q);
+			const int32_t f = (int32_t)g_be32(bytes, q + fld);
+			return l >= (int32_t)fld && l <= ZKB_MAX_PACKET && q + 4 + (uint64_t)l > send &&
+			    (server ? op_known(f) : err_known(f));
+		}
+		q = n2;
+	}
+	return true;
+}
+
+/* word J (0..11) of the 48-byte window held in three uint4 registers */
+template <int J>
+__device__ __forceinline__ uint32_t win_word(const uint4 &a, const uint4 &b, const uint4 &c)
+{
+	if constexpr (J == 0) return a.x; else if constexpr (J == 1) return a.y;
+	else if constexpr (J == 2) return a.z; else if constexpr (J == 3) return a.w;
+	else if constexpr (J == 4) return b.x; else if constexpr (J == 5) return b.y;
+	else if constexpr (J == 6) return b.z; else if constexpr (J == 7) return b.w;
+	else if constexpr (J == 8) return c.x; else if constexpr (J == 9) return c.y;
+	else if constexpr (J == 10) return c.z; else return c.w;
+}
+/* big-endian int32 at byte K (0..43) of the window */
+template <int K>
+__device__ __forceinline__ int32_t win_be32(const uint4 &a, const uint4 &b, const uint4 &c)
+{
+	return (int32_t)bswap32(__funnelshift_r(win_word<K / 4>(a, b, c), win_word<K / 4 + 1>(a, b, c), (K % 4) * 8));
+}
+
+struct GuessCtx {
+	const uint8_t *bytes;
+	uint64_t lim, send;
+	bool server;
+};
+
+/* local test of the candidate at byte K of the window that starts at absolute position blk:
+ * sane length that fits the session, err code / opcode where the header would have it */
+template <int K>
+__device__ __forceinline__ uint32_t guess_at(const GuessCtx &g, uint64_t blk, uint32_t m, const uint4 &v0,
+    const uint4 &v1, const uint4 &v2)
+{
+	if (!((m >> K) & 1)) return 0;
+	const uint64_t p = blk + K;
+	if (p >= g.lim) return 0;
+	const int32_t len = win_be32<K>(v0, v1, v2);
+	if (len < (g.server ? 8 : 16) || len > ZKB_MAX_PACKET) return 0;
+	if (p + 4 + (uint64_t)len > g.send) return 0;
+	const int32_t f = g.server ? win_be32<K + 8>(v0, v1, v2) : win_be32<K + 16>(v0, v1, v2);
+	if (g.server ? !op_known(f) : !err_known(f)) return 0;
+	return 1u << K;
+}
+
+/* First position in [gs, min(ge, send)) that looks like a frame start.  The granule is
+ * scanned 16 bytes per load, 64 bytes per round: positions that pass the local test are
+ * collected in a bit mask, then checked by following the chain three more frames.  Keeping
+ * the far (DRAM-latency) checks out of the scan loop lets the lanes of a warp, which scan
+ * different granules, issue them together instead of one lane at a time. */
 __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uint64_t ge, uint64_t send)
 {
-	bool server = a.sess_flags && (a.sess_flags[s] & ZKB_SESS_SERVER);
-	uint64_t lim = ge < send ? ge : send;
-	for (uint64_t p = gs; p < lim; ++p) {
-		uint64_t next;
-		if (!header_plausible(a.bytes, p, send, server, next)) continue;
-		if (next == send || next + 4 > send) return p;
-		if (len_ok((int32_t)g_be32(a.bytes, next))) return p;
+	GuessCtx g;
+	g.bytes = a.bytes;
+	g.server = a.sess_flags && (a.sess_flags[s] & ZKB_SESS_SERVER);
+	g.lim = ge < send ? ge : send;
+	g.send = send;
+	const uint64_t padend = (a.nbytes + 15) & ~15ull;
+	uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0, v2 = v0;
+	if (gs + 16 <= padend) v0 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs));
+	if (gs + 32 <= padend) v1 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs + 16));
+	for (uint64_t seg = gs; seg < g.lim; seg += 128) {
+		/* phase 1: local tests only, the lanes of a warp stay in step */
+		uint64_t cand_lo = 0, cand_hi = 0;
+#pragma unroll 1
+		for (int q = 0; q < 8; ++q) {
+			const uint64_t blk = seg + 16 * q;
+			v2 = make_uint4(0, 0, 0, 0);
+			if (blk + 48 <= padend) v2 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + blk + 32));
+			/* bytes <= 1 in the first 16 (a length <= 16 MiB starts with 0x00 or 0x01); the
+			 * zero-byte trick may flag extra bytes, every hit is re-checked in guess_at */
+			uint32_t m = 0;
+			{
+				const uint32_t ww[4] = { v0.x, v0.y, v0.z, v0.w };
+#pragma unroll
+				for (int j = 0; j < 4; ++j) {
+					uint32_t t = ww[j] & 0xFEFEFEFEu;
+					uint32_t z = (t - 0x01010101u) & ~t & 0x80808080u;
+					m |= (((z >> 7) & 1) | ((z >> 14) & 2) | ((z >> 21) & 4) | ((z >> 28) & 8)) << (4 * j);
+				}
+			}
+			if (m && blk < g.lim) {
+				uint32_t c = guess_at<0>(g, blk, m, v0, v1, v2) | guess_at<1>(g, blk, m, v0, v1, v2) |
+				    guess_at<2>(g, blk, m, v0, v1, v2) | guess_at<3>(g, blk, m, v0, v1, v2) |
+				    guess_at<4>(g, blk, m, v0, v1, v2) | guess_at<5>(g, blk, m, v0, v1, v2) |
+				    guess_at<6>(g, blk, m, v0, v1, v2) | guess_at<7>(g, blk, m, v0, v1, v2) |
+				    guess_at<8>(g, blk, m, v0, v1, v2) | guess_at<9>(g, blk, m, v0, v1, v2) |
+				    guess_at<10>(g, blk, m, v0, v1, v2) | guess_at<11>(g, blk, m, v0, v1, v2) |
+				    guess_at<12>(g, blk, m, v0, v1, v2) | guess_at<13>(g, blk, m, v0, v1, v2) |
+				    guess_at<14>(g, blk, m, v0, v1, v2) | guess_at<15>(g, blk, m, v0, v1, v2);
+				if (q < 4) cand_lo |= (uint64_t)c << (16 * q);
+				else cand_hi |= (uint64_t)c << (16 * (q - 4));
+			}
+			v0 = v1; v1 = v2;
+		}
+		/* phase 2: the far checks, candidate by candidate in stream order */
+#pragma unroll 1
+		for (int half = 0; half < 2; ++half) {
+			uint64_t cand = half ? cand_hi : cand_lo;
+			while (cand) {
+				const int k = __ffsll((long long)cand) - 1;
+				cand &= cand - 1;
+				const uint64_t p = seg + 64 * half + (uint64_t)k;
+				const int32_t len = (int32_t)g_be32(a.bytes, p);
+				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, 3)) return p;
+			}
+		}
 	}
 	return ZK_NONE;
 }
@@ -218,6 +338,11 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		uint32_t s = sf - 1;
 		uint64_t send = __ldg(a.sess_off + sf);
 		assumed = (MODE == MODE_SPEC) ? guess_entry(a, s, gs, ge, send) : a.g_carry[g];
+	}
+	if (MODE == MODE_SPEC) __syncwarp();   /* lanes finish guessing at different times: walk together */
+	if (cont) {
+		uint32_t s = sf - 1;
+		uint64_t send = __ldg(a.sess_off + sf);
 		if (assumed >= gs && assumed < ge) {
 			touched = true;
 			pos = walk_chain<MODE>(a, s, assumed, send, ge, count, base);
@@ -230,25 +355,38 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		if (MODE == MODE_EMIT) a.sess_first[s] = base + count;
 		pos = walk_chain<MODE>(a, s, so, __ldg(a.sess_off + s + 1), ge, count, base);
 	}
+	const uint64_t out = touched ? pos : ZK_INHERIT;
 	if (MODE == MODE_EMIT) {
-		if (count != a.g_cnt[g]) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
+		if (count != a.g_cnt[(size_t)a.g_sel[g] * a.n_gran + g]) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
+	} else if (MODE == MODE_SPEC) {
+		a.g_assumed[g] = assumed; a.g_out[g] = out; a.g_cnt[g] = count;
+		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = out; a.g_cnt[a.n_gran + g] = count;
+		a.g_sel[g] = 0;
 	} else {
-		a.g_assumed[g] = assumed;
-		a.g_out[g] = touched ? pos : ZK_INHERIT;
-		a.g_cnt[g] = count;
+		/* Every dirty granule re-walks from its carried position, but the result only
+		 * replaces the guess-based one in the next scan if that position can be trusted:
+		 * the granule that produced it is itself consistent, and it does not land in an
+		 * earlier granule.  Otherwise the scan keeps using the walk from the granule's own
+		 * guess, whose exit is usually right even when its entry was not, so one bad guess
+		 * cannot push an error wave down the stream.  The lowest dirty granule always
+		 * qualifies, so every iteration makes progress. */
+		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = out; a.g_cnt[a.n_gran + g] = count;
+		const uint32_t src = a.g_src[g];
+		const bool trusted = !(src && a.g_dirty[src - 1]) && !(assumed != ZK_NONE && assumed < gs);
+		a.g_sel[g] = trusted ? 1 : 0;
 	}
 }
 
 /* ---- scan over granules: value = (last exit that is not INHERIT, sum of counts) ------ */
 
-struct ScanVal { uint64_t v; uint32_t c; uint32_t pad; };
+struct ScanVal { uint64_t v; uint32_t c; uint32_t src; };
 
 __device__ __forceinline__ ScanVal sv_comb(ScanVal l, ScanVal r)
 {
 	ScanVal o;
 	o.v = (r.v != ZK_INHERIT) ? r.v : l.v;
+	o.src = (r.v != ZK_INHERIT) ? r.src : l.src;
 	o.c = l.c + r.c;
-	o.pad = 0;
 	return o;
 }
 __device__ __forceinline__ ScanVal sv_shfl_up(ScanVal x, int d)
@@ -256,7 +394,7 @@ __device__ __forceinline__ ScanVal sv_shfl_up(ScanVal x, int d)
 	ScanVal o;
 	o.v = __shfl_up_sync(0xffffffffu, x.v, d);
 	o.c = __shfl_up_sync(0xffffffffu, x.c, d);
-	o.pad = 0;
+	o.src = __shfl_up_sync(0xffffffffu, x.src, d);
 	return o;
 }
 
@@ -272,7 +410,7 @@ __device__ ScanVal block_scan_incl(ScanVal x, ScanVal *total, ScanVal *s_w /* [3
 	}
 	if (lane == 31) s_w[wid] = x;
 	__syncthreads();
-	ScanVal pre; pre.v = ZK_INHERIT; pre.c = 0; pre.pad = 0;
+	ScanVal pre; pre.v = ZK_INHERIT; pre.c = 0; pre.src = 0;
 	ScanVal tot = pre;
 	const int nw = blockDim.x >> 5;
 	for (int w = 0; w < nw; ++w) {
@@ -288,8 +426,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 {
 	__shared__ ScanVal s_w[32];
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
-	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.pad = 0;
-	if (g < a.n_gran) { x.v = a.g_out[g]; x.c = a.g_cnt[g]; }
+	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0;
+	if (g < a.n_gran) {
+		const size_t i = (size_t)a.g_sel[g] * a.n_gran + g;
+		x.v = a.g_out[i]; x.c = a.g_cnt[i]; x.src = g + 1;
+	}
 	ScanVal tot;
 	block_scan_incl(x, &tot, s_w);
 	if (threadIdx.x == 0) blk[blockIdx.x] = tot;
@@ -299,10 +440,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint32_t nblk)
 {
 	__shared__ ScanVal s_w[32];
-	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.pad = 0;
+	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.src = 0;
 	for (uint32_t b0 = 0; b0 < nblk; b0 += SCAN_THREADS) {
 		uint32_t i = b0 + threadIdx.x;
-		ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.pad = 0;
+		ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0;
 		if (i < nblk) x = blk[i];
 		ScanVal tot;
 		ScanVal inc = block_scan_incl(x, &tot, s_w);
@@ -312,7 +453,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint
 		if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
 		__syncthreads();
 		ScanVal ex;
-		if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.pad = 0; }
+		if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; }
 		else if ((threadIdx.x & 31) == 0) ex = s_last[(threadIdx.x >> 5) - 1];
 		else ex = prev;
 		if (i < nblk) blk[i] = sv_comb(carry, ex);
@@ -326,15 +467,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	__shared__ ScanVal s_w[32];
 	__shared__ ScanVal s_last[32];
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
-	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.pad = 0;
-	if (g < a.n_gran) { x.v = a.g_out[g]; x.c = a.g_cnt[g]; }
+	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0;
+	if (g < a.n_gran) {
+		const size_t i = (size_t)a.g_sel[g] * a.n_gran + g;
+		x.v = a.g_out[i]; x.c = a.g_cnt[i]; x.src = g + 1;
+	}
 	ScanVal tot;
 	ScanVal inc = block_scan_incl(x, &tot, s_w);
 	ScanVal prev = sv_shfl_up(inc, 1);
 	if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
 	__syncthreads();
 	ScanVal ex;
-	if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.pad = 0; }
+	if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; }
 	else if ((threadIdx.x & 31) == 0) ex = s_last[(threadIdx.x >> 5) - 1];
 	else ex = prev;
 	ex = sv_comb(blk[blockIdx.x], ex);
@@ -344,13 +488,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	uint64_t carry = (ex.v == ZK_INHERIT) ? ZK_NONE : ex.v;
 	a.g_carry[g] = carry;
 	a.g_base[g] = ex.c;
-	/* consistent iff both name the same in-granule position, or neither names one */
-	uint64_t as = a.g_assumed[g];
-	uint64_t na = (as >= gs && as < ge) ? as : ZK_NONE;
-	uint64_t nc = (carry >= gs && carry < ge) ? carry : ZK_NONE;
-	uint8_t dirty = (na != nc);
+	a.g_src[g] = (ex.v == ZK_INHERIT) ? 0u : ex.src;
+	/* a walk is consistent with the carry iff both name the same in-granule position, or
+	 * neither names one; pick whichever version is, else the granule is dirty */
+	const uint64_t nc = (carry >= gs && carry < ge) ? carry : ZK_NONE;
+	const uint64_t a0 = a.g_assumed[g], a1 = a.g_assumed[a.n_gran + g];
+	const uint64_t n0 = (a0 >= gs && a0 < ge) ? a0 : ZK_NONE;
+	const uint64_t n1 = (a1 >= gs && a1 < ge) ? a1 : ZK_NONE;
+	const uint8_t old = a.g_sel[g];
+	uint8_t dirty = 0, sel = old;
+	if ((old ? n1 : n0) == nc) sel = old;
+	else if (n0 == nc) sel = 0;
+	else if (n1 == nc) sel = 1;
+	else dirty = 1;
 	a.g_dirty[g] = dirty;
-	if (dirty) atomicAdd(&a.ctrl->n_dirty, 1u);
+	a.g_sel[g] = sel;
+	/* a changed selection changes what the scan saw: not converged yet */
+	if (dirty || sel != old) atomicAdd(&a.ctrl->n_dirty, 1u);
+	if (dirty) atomicAdd(&a.ctrl->n_rewalk, 1u);
 	if (g == a.n_gran - 1) a.ctrl->n_frames = (unsigned long long)ex.c + x.c;
 }
 
@@ -390,12 +545,10 @@ struct DecArgs {
 	const uint32_t *g_base;
 	uint32_t        glog2;
 	uint32_t        n_gran;
-	uint32_t        n_tiles;
+	uint32_t        n_chunks;
 	uint64_t        n_frames;
 	zkb_decoded     o;
-	uint32_t       *lb_flag;      /* [n_tiles] */
-	uint32_t       *lb_agg;       /* [n_tiles][4] */
-	uint32_t       *lb_pfx;       /* [n_tiles][4] */
+	uint4          *lb;           /* [n_chunks] { state, stat rows, buf rows, acl rows } */
 	zk_ctrl        *ctrl;
 };
 
@@ -510,14 +663,65 @@ struct Parsed {
 };
 enum { VEC_NONE = 0, VEC_STR1 = 1, VEC_ACL = 2, VEC_STR3 = 3 };
 
+/* ---- per-warp chunk state in shared memory ------------------------------------------
+ * A decode warp owns one 8 KiB chunk of the batch: the chunk plus a short overhang is
+ * staged in `tile`, and every side-table row the chunk's frames produce is first recorded
+ * as one bit in a bitmap indexed by the 4-byte slot that holds the field's first byte
+ * (length prefix of a buffer/ustring, perms word of an ACL entry, first byte of a Stat).
+ * Two fields never start in the same slot, and slot order is stream order, so compacting a
+ * bitmap yields the chunk's rows already in (frame, read order) order.  sub0/sub1 keep the
+ * low two bits of the byte position. */
+#define ZK_CHUNK_LOG2  13
+#define ZK_CHUNK       (1u << ZK_CHUNK_LOG2)
+#define ZK_OVER        768u
+#define ZK_WIN         (ZK_CHUNK + ZK_OVER)
+#define ZK_SLOTS       (ZK_WIN / 4)
+#define ZK_BMW         (ZK_SLOTS / 32)
+#define ZK_DEC_WARPS   4
+
+struct ChunkSm {
+	uint8_t  tile[ZK_WIN + 16];
+	uint32_t m_buf[ZK_BMW], m_acl[ZK_BMW], m_stat[ZK_BMW];
+	uint32_t sub0[ZK_BMW], sub1[ZK_BMW];
+	uint32_t fstart[ZK_BMW];       /* slots where a frame's length prefix starts */
+	uint16_t fpre[ZK_BMW + 2];     /* exclusive prefix of popc(fstart[w]) */
+};
+
+enum { WALK_COUNT = 0, WALK_EMIT = 1, WALK_MARK = 2 };
+enum { FAST_MARK = 1, FAST_UNMARK = 2 };
+
+__device__ __forceinline__ uint32_t sm_be32(const uint8_t *tile, uint32_t rel)
+{
+	const uint32_t *w = reinterpret_cast<const uint32_t *>(tile + (rel & ~3u));
+	return bswap32(__funnelshift_r(w[0], w[1], (rel & 3u) * 8));
+}
+
+template <int M>
+__device__ __forceinline__ void mark_pos(ChunkSm &c, uint32_t *bm, uint32_t prel)
+{
+	const uint32_t w = prel >> 7, bit = 1u << ((prel >> 2) & 31);
+	if (M == FAST_MARK) {
+		atomicOr(&bm[w], bit);
+		if (prel & 1) atomicOr(&c.sub0[w], bit);
+		if (prel & 2) atomicOr(&c.sub1[w], bit);
+	} else {
+		atomicAnd(&bm[w], ~bit);
+		atomicAnd(&c.sub0[w], ~bit);
+		atomicAnd(&c.sub1[w], ~bit);
+	}
+}
+
 struct SideRows {
 	zkb_decoded o;
 	uint32_t frame;
 	uint32_t buf_row, acl_row;
+	ChunkSm *cs;        /* WALK_MARK: where to mark */
+	uint32_t payrel;    /* WALK_MARK: payload byte 0 relative to the tile */
 };
 
-/* vector<ustring> (zk-buffer.js:334-337,238-252).  EMIT = false: validate and count. */
-template <bool EMIT>
+/* vector<ustring> (zk-buffer.js:334-337,238-252).  WALK_COUNT validates and counts,
+ * WALK_EMIT writes BUF rows directly, WALK_MARK records them in the chunk bitmaps. */
+template <int MODE>
 __device__ bool walk_strvec(Cur &c, int32_t &n_out, uint32_t &n_buf, SideRows *sr)
 {
 	int32_t count;
@@ -526,13 +730,15 @@ __device__ bool walk_strvec(Cur &c, int32_t &n_out, uint32_t &n_buf, SideRows *s
 	for (int32_t i = 0; i < count; ++i) {
 		uint32_t pos; int32_t len;
 		if (!c_buf(c, ZKB_F_ELEM, pos, len)) return false;
-		if (EMIT) {
+		if (MODE == WALK_EMIT) {
 			uint64_t row = sr->buf_row++;
 			if (row < sr->o.cap_buf) {
 				sr->o.buf_frame[row] = sr->frame;
 				sr->o.buf_off[row] = c.pay + pos;
 				sr->o.buf_len[row] = len;
 			}
+		} else if (MODE == WALK_MARK) {
+			mark_pos<FAST_MARK>(*sr->cs, sr->cs->m_buf, sr->payrel + pos - 4);
 		}
 		n_buf++;
 	}
@@ -540,7 +746,7 @@ __device__ bool walk_strvec(Cur &c, int32_t &n_out, uint32_t &n_buf, SideRows *s
 }
 
 /* readACL (zk-buffer.js:372-382): count x { perms, scheme, id } */
-template <bool EMIT>
+template <int MODE>
 __device__ bool walk_acl(Cur &c, int32_t &n_out, uint32_t &n_buf, uint32_t &n_acl, SideRows *sr)
 {
 	int32_t count;
@@ -548,10 +754,11 @@ __device__ bool walk_acl(Cur &c, int32_t &n_out, uint32_t &n_buf, uint32_t &n_ac
 	n_out = count > 0 ? count : 0;
 	for (int32_t i = 0; i < count; ++i) {
 		int32_t perms; uint32_t p0, p1; int32_t l0, l1;
+		const uint32_t at = c.cur;
 		if (!c_int(c, ZKB_F_ACL_PERMS, perms)) return false;
 		if (!c_buf(c, ZKB_F_ACL_SCHEME, p0, l0)) return false;
 		if (!c_buf(c, ZKB_F_ACL_ID, p1, l1)) return false;
-		if (EMIT) {
+		if (MODE == WALK_EMIT) {
 			uint64_t ar = sr->acl_row++;
 			if (ar < sr->o.cap_acl) { sr->o.acl_frame[ar] = sr->frame; sr->o.acl_perms[ar] = perms; }
 			uint64_t row = sr->buf_row; sr->buf_row += 2;
@@ -561,6 +768,10 @@ __device__ bool walk_acl(Cur &c, int32_t &n_out, uint32_t &n_buf, uint32_t &n_ac
 			if (row + 1 < sr->o.cap_buf) {
 				sr->o.buf_frame[row + 1] = sr->frame; sr->o.buf_off[row + 1] = c.pay + p1; sr->o.buf_len[row + 1] = l1;
 			}
+		} else if (MODE == WALK_MARK) {
+			mark_pos<FAST_MARK>(*sr->cs, sr->cs->m_acl, sr->payrel + at);
+			mark_pos<FAST_MARK>(*sr->cs, sr->cs->m_buf, sr->payrel + p0 - 4);
+			mark_pos<FAST_MARK>(*sr->cs, sr->cs->m_buf, sr->payrel + p1 - 4);
 		}
 		n_buf += 2;
 		n_acl++;
@@ -610,7 +821,7 @@ __device__ void parse_response(Cur &c, Parsed &p, int &opcode, const DecArgs &a,
 	case ZKB_OP_GET_CHILDREN:
 	case ZKB_OP_GET_CHILDREN2:
 		p.vec_kind = VEC_STR1; p.vec_pos = c.cur;
-		if (!walk_strvec<false>(c, p.a0, p.n_buf, nullptr)) return;
+		if (!walk_strvec<WALK_COUNT>(c, p.a0, p.n_buf, nullptr)) return;
 		if (op == ZKB_OP_GET_CHILDREN2) { if (!c_stat(c, p.stat_pos)) return; p.n_stat = 1; }
 		break;
 	case ZKB_OP_CREATE:
@@ -618,7 +829,7 @@ __device__ void parse_response(Cur &c, Parsed &p, int &opcode, const DecArgs &a,
 		break;
 	case ZKB_OP_GET_ACL:
 		p.vec_kind = VEC_ACL; p.vec_pos = c.cur;
-		if (!walk_acl<false>(c, p.a0, p.n_buf, p.n_acl, nullptr)) return;
+		if (!walk_acl<WALK_COUNT>(c, p.a0, p.n_buf, p.n_acl, nullptr)) return;
 		if (!c_stat(c, p.stat_pos)) return;
 		p.n_stat = 1;
 		break;
@@ -669,7 +880,7 @@ __device__ void parse_request(Cur &c, Parsed &p, int &opcode)
 		if (!fixed_buf(c, ZKB_F_PATH, p)) return;
 		if (!fixed_buf(c, ZKB_F_DATA, p)) return;
 		p.vec_kind = VEC_ACL; p.vec_pos = c.cur;
-		if (!walk_acl<false>(c, p.a1, p.n_buf, p.n_acl, nullptr)) return;
+		if (!walk_acl<WALK_COUNT>(c, p.a1, p.n_buf, p.n_acl, nullptr)) return;
 		c_int(c, ZKB_F_FLAGS, p.a0);
 		break;
 	case ZKB_OP_DELETE:
@@ -688,9 +899,9 @@ __device__ void parse_request(Cur &c, Parsed &p, int &opcode)
 	case ZKB_OP_SET_WATCHES:
 		if (!c_long(c, ZKB_F_REL_ZXID, p.zxid)) return;
 		p.vec_kind = VEC_STR3; p.vec_pos = c.cur;
-		if (!walk_strvec<false>(c, p.a0, p.n_buf, nullptr)) return;
-		if (!walk_strvec<false>(c, p.a1, p.n_buf, nullptr)) return;
-		walk_strvec<false>(c, p.err, p.n_buf, nullptr);
+		if (!walk_strvec<WALK_COUNT>(c, p.a0, p.n_buf, nullptr)) return;
+		if (!walk_strvec<WALK_COUNT>(c, p.a1, p.n_buf, nullptr)) return;
+		walk_strvec<WALK_COUNT>(c, p.err, p.n_buf, nullptr);
 		break;
 	default:
 		c.fail = DETAIL(ZKB_CAUSE_UNSUPPORTED, ZKB_F_OPCODE);   /* :91-92 */
@@ -765,7 +976,7 @@ __device__ void emit_side(const Rd &rd, const DecArgs &a, uint64_t foff, int32_t
 		o.pzxid[stat_row] = rd.be64(q + 60);
 	}
 	SideRows sr;
-	sr.o = o; sr.frame = frame; sr.buf_row = buf_row; sr.acl_row = acl_row;
+	sr.o = o; sr.frame = frame; sr.buf_row = buf_row; sr.acl_row = acl_row; sr.cs = nullptr; sr.payrel = 0;
 	if (p.n_fixed > 0) {
 		uint64_t row = sr.buf_row++;
 		if (row < o.cap_buf) {
@@ -783,197 +994,497 @@ __device__ void emit_side(const Rd &rd, const DecArgs &a, uint64_t foff, int32_t
 		c.rd = &rd; c.pay = pay; c.size = (uint32_t)flen; c.cur = p.vec_pos; c.fail = 0;
 		int32_t n; uint32_t nb = 0, na = 0;
 		if (p.vec_kind == VEC_STR1) {
-			walk_strvec<true>(c, n, nb, &sr);
+			walk_strvec<WALK_EMIT>(c, n, nb, &sr);
 		} else if (p.vec_kind == VEC_ACL) {
-			walk_acl<true>(c, n, nb, na, &sr);
+			walk_acl<WALK_EMIT>(c, n, nb, na, &sr);
 		} else {
-			walk_strvec<true>(c, n, nb, &sr);
-			walk_strvec<true>(c, n, nb, &sr);
-			walk_strvec<true>(c, n, nb, &sr);
+			walk_strvec<WALK_EMIT>(c, n, nb, &sr);
+			walk_strvec<WALK_EMIT>(c, n, nb, &sr);
+			walk_strvec<WALK_EMIT>(c, n, nb, &sr);
 		}
 	}
 }
 
-/* exclusive scan of three counters over the block; tot[] = block totals */
-__device__ void block_scan3(uint32_t v0, uint32_t v1, uint32_t v2, uint32_t &e0, uint32_t &e1,
-    uint32_t &e2, uint32_t tot[3], uint32_t (*s_w)[ZK_DECODE_THREADS / 32])
+/* ================================================================================== */
+/* optimistic fast path: well-formed frames that lie completely inside the staged tile.
+ * Same reads in the same order as the generic readers, but no exception bookkeeping: any
+ * irregularity makes the function return false, the marks it made are undone by running it
+ * again in FAST_UNMARK mode, and the frame is handed to parse_frame() for the exact answer. */
+
+struct FrameCols {
+	uint32_t meta;
+	int32_t  xid, err, a0, a1;
+	int64_t  zxid;
+};
+
+struct FC {
+	ChunkSm *c;
+	uint32_t pr;     /* payload byte 0, tile-relative */
+	uint32_t size;
+	uint32_t cur;
+	__device__ __forceinline__ bool i32(int32_t &v)
+	{
+		if (cur + 4 > size) return false;
+		v = (int32_t)sm_be32(c->tile, pr + cur);
+		cur += 4;
+		return true;
+	}
+	template <int M>
+	__device__ __forceinline__ bool buf(uint32_t *bm)
+	{
+		if (cur + 4 > size) return false;
+		const int32_t l = (int32_t)sm_be32(c->tile, pr + cur);
+		const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+		if (cur + 4 + ul > size) return false;
+		mark_pos<M>(*c, bm, pr + cur);
+		cur += 4 + ul;
+		return true;
+	}
+	template <int M>
+	__device__ __forceinline__ bool stat()
+	{
+		if (cur + 68 > size) return false;
+		mark_pos<M>(*c, c->m_stat, pr + cur);
+		cur += 68;
+		return true;
+	}
+	template <int M>
+	__device__ __forceinline__ bool strvec(int32_t &n)
+	{
+		int32_t count;
+		if (!i32(count)) return false;
+		for (int32_t i = 0; i < count; ++i)
+			if (!buf<M>(c->m_buf)) return false;
+		n = count > 0 ? count : 0;
+		return true;
+	}
+	template <int M>
+	__device__ __forceinline__ bool acl(int32_t &n)
+	{
+		int32_t count;
+		if (!i32(count)) return false;
+		for (int32_t i = 0; i < count; ++i) {
+			if (cur + 4 > size) return false;
+			const uint32_t at = pr + cur;
+			cur += 4;
+			if (!buf<M>(c->m_buf)) return false;
+			if (!buf<M>(c->m_buf)) return false;
+			mark_pos<M>(*c, c->m_acl, at);
+		}
+		n = count > 0 ? count : 0;
+		return true;
+	}
+};
+
+/* readResponse (zk-buffer.js:281-331), frames with a body the reference accepts */
+/* returns 1 = decoded; 0 = not decodable here, marks may have been made; -1 = not decodable
+ * here and nothing was marked */
+template <int M>
+__device__ int fast_response(ChunkSm &c, const DecArgs &a, uint32_t pr, uint32_t size, uint32_t s,
+    FrameCols &o)
 {
-	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	uint32_t i0 = v0, i1 = v1, i2 = v2;
+	if (size < 16) return -1;
+	const uint8_t *t = c.tile;
+	const int32_t xid = (int32_t)sm_be32(t, pr);
+	const int32_t err = (int32_t)sm_be32(t, pr + 12);
+	int op = special_xid(xid);
+	if (op == ZKB_OP_NONE && a.xt_ops) {
+		int64_t idx = (int64_t)xid - (int64_t)__ldg(a.xt_base + s);
+		if (idx >= 0 && idx < (int64_t)__ldg(a.xt_count + s))
+			op = __ldg(a.xt_ops + __ldg(a.xt_off + s) + (uint64_t)idx);
+	}
+	if (op == ZKB_OP_NONE) return -1;
+	o.a0 = 0; o.a1 = 0;
+	if (err == 0) {
+		FC f; f.c = &c; f.pr = pr; f.size = size; f.cur = 16;
+		switch (op) {
+		case ZKB_OP_GET_CHILDREN:
+			if (!f.strvec<M>(o.a0)) return false;
+			break;
+		case ZKB_OP_GET_CHILDREN2:
+			if (!f.strvec<M>(o.a0)) return false;
+			if (!f.stat<M>()) return false;
+			break;
+		case ZKB_OP_CREATE:
+			if (!f.buf<M>(c.m_buf)) return false;
+			break;
+		case ZKB_OP_GET_ACL:
+			if (!f.acl<M>(o.a0)) return false;
+			if (!f.stat<M>()) return false;
+			break;
+		case ZKB_OP_GET_DATA:
+			if (!f.buf<M>(c.m_buf)) return false;
+			if (!f.stat<M>()) return false;
+			break;
+		case ZKB_OP_NOTIFICATION:
+			if (!f.i32(o.a0)) return false;
+			if (!f.i32(o.a1)) return false;
+			if (!f.buf<M>(c.m_buf)) return false;
+			break;
+		case ZKB_OP_EXISTS:
+		case ZKB_OP_SET_DATA:
+			if (!f.stat<M>()) return false;
+			break;
+		case ZKB_OP_SET_WATCHES:
+		case ZKB_OP_PING:
+		case ZKB_OP_SYNC:
+		case ZKB_OP_DELETE:
+		case ZKB_OP_CLOSE_SESSION:
+			break;
+		default:
+			return -1;
+		}
+	}
+	o.xid = xid;
+	o.err = err;
+	o.zxid = (int64_t)(((uint64_t)sm_be32(t, pr + 4) << 32) | (uint64_t)sm_be32(t, pr + 8));
+	o.meta = ZKB_ST_OK | ((uint32_t)(uint8_t)(int8_t)op << 8) | ((uint32_t)ZKB_KIND_RESPONSE << 16);
+	return 1;
+}
+
+/* readRequest (zk-buffer.js:58-95,138-253), the opcodes it can read */
+template <int M>
+__device__ int fast_request(ChunkSm &c, uint32_t pr, uint32_t size, FrameCols &o)
+{
+	if (size < 8) return -1;
+	const uint8_t *t = c.tile;
+	const int32_t xid = (int32_t)sm_be32(t, pr);
+	const int32_t op = (int32_t)sm_be32(t, pr + 4);
+	FC f; f.c = &c; f.pr = pr; f.size = size; f.cur = 8;
+	o.a0 = 0; o.a1 = 0; o.err = 0; o.zxid = 0;
+	switch (op) {
+	case ZKB_OP_GET_CHILDREN:
+	case ZKB_OP_GET_CHILDREN2:
+	case ZKB_OP_GET_DATA:
+	case ZKB_OP_EXISTS: {
+		if (!f.buf<M>(c.m_buf)) return false;
+		if (!(f.cur < size)) return false;
+		const uint32_t b = t[pr + f.cur];
+		if (b > 1) return false;
+		o.a0 = (int32_t)b;
+		break;
+	}
+	case ZKB_OP_CREATE:
+		if (!f.buf<M>(c.m_buf)) return false;
+		if (!f.buf<M>(c.m_buf)) return false;
+		if (!f.acl<M>(o.a1)) return false;
+		if (!f.i32(o.a0)) return false;
+		break;
+	case ZKB_OP_DELETE:
+		if (!f.buf<M>(c.m_buf)) return false;
+		if (!f.i32(o.a0)) return false;
+		break;
+	case ZKB_OP_GET_ACL:
+	case ZKB_OP_SYNC:
+		if (!f.buf<M>(c.m_buf)) return false;
+		break;
+	case ZKB_OP_SET_DATA:
+		if (!f.buf<M>(c.m_buf)) return false;
+		if (!f.buf<M>(c.m_buf)) return false;
+		if (!f.i32(o.a0)) return false;
+		break;
+	case ZKB_OP_SET_WATCHES:
+		if (size < 16) return false;
+		o.zxid = (int64_t)(((uint64_t)sm_be32(t, pr + 8) << 32) | (uint64_t)sm_be32(t, pr + 12));
+		f.cur = 16;
+		if (!f.strvec<M>(o.a0)) return false;
+		if (!f.strvec<M>(o.a1)) return false;
+		if (!f.strvec<M>(o.err)) return false;
+		break;
+	default:
+		return -1;   /* PING, CLOSE_SESSION and unknown types throw in the reference */
+	}
+	o.xid = xid;
+	o.meta = ZKB_ST_OK | ((uint32_t)(uint8_t)(int8_t)op << 8) | ((uint32_t)ZKB_KIND_REQUEST << 16);
+	return 1;
+}
+
+/* A frame the generic parser accepted and that lies inside the tile: record its rows */
+__device__ void mark_from_parsed(ChunkSm &c, const Rd &rd, uint32_t payrel, uint64_t pay, int32_t flen,
+    const Parsed &p)
+{
+	if (p.n_stat) mark_pos<FAST_MARK>(c, c.m_stat, payrel + p.stat_pos);
+	if (p.n_fixed > 0) mark_pos<FAST_MARK>(c, c.m_buf, payrel + p.fb0_pos - 4);
+	if (p.n_fixed > 1) mark_pos<FAST_MARK>(c, c.m_buf, payrel + p.fb1_pos - 4);
+	if (p.vec_kind != VEC_NONE) {
+		SideRows sr;
+		sr.cs = &c; sr.payrel = payrel;
+		Cur cu;
+		cu.rd = &rd; cu.pay = pay; cu.size = (uint32_t)flen; cu.cur = p.vec_pos; cu.fail = 0;
+		int32_t n; uint32_t nb = 0, na = 0;
+		if (p.vec_kind == VEC_STR1) {
+			walk_strvec<WALK_MARK>(cu, n, nb, &sr);
+		} else if (p.vec_kind == VEC_ACL) {
+			walk_acl<WALK_MARK>(cu, n, nb, na, &sr);
+		} else {
+			walk_strvec<WALK_MARK>(cu, n, nb, &sr);
+			walk_strvec<WALK_MARK>(cu, n, nb, &sr);
+			walk_strvec<WALK_MARK>(cu, n, nb, &sr);
+		}
+	}
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v)
+{
+	for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+	return v;
+}
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane)
+{
 	for (int d = 1; d < 32; d <<= 1) {
-		uint32_t y0 = __shfl_up_sync(0xffffffffu, i0, d);
-		uint32_t y1 = __shfl_up_sync(0xffffffffu, i1, d);
-		uint32_t y2 = __shfl_up_sync(0xffffffffu, i2, d);
-		if (lane >= d) { i0 += y0; i1 += y1; i2 += y2; }
+		uint32_t y = __shfl_up_sync(0xffffffffu, v, d);
+		if (lane >= d) v += y;
 	}
-	if (lane == 31) { s_w[0][wid] = i0; s_w[1][wid] = i1; s_w[2][wid] = i2; }
-	__syncthreads();
-	uint32_t p0 = 0, p1 = 0, p2 = 0, t0 = 0, t1 = 0, t2 = 0;
-	for (int w = 0; w < ZK_DECODE_THREADS / 32; ++w) {
-		if (w == wid) { p0 = t0; p1 = t1; p2 = t2; }
-		t0 += s_w[0][w]; t1 += s_w[1][w]; t2 += s_w[2][w];
-	}
-	__syncthreads();
-	e0 = p0 + i0 - v0; e1 = p1 + i1 - v1; e2 = p2 + i2 - v2;
-	tot[0] = t0; tot[1] = t1; tot[2] = t2;
+	return v;
 }
 
 #define ZK_SPIN_LIMIT (1u << 26)
 
-__global__ void __launch_bounds__(ZK_DECODE_THREADS) k_decode(DecArgs a)
+/* One warp per 8 KiB chunk; warps never wait for each other except through the look-back. */
+__global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 {
-	__shared__ __align__(16) uint8_t s_tile[ZK_TILE_BYTES + ZK_TILE_OVERHANG + 16];
-	__shared__ uint32_t s_w[3][ZK_DECODE_THREADS / 32];
-	__shared__ uint32_t s_bc[4];
-	const uint32_t tid = threadIdx.x;
+	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
+	const uint32_t lane = threadIdx.x & 31;
+	ChunkSm &c = sm_all[threadIdx.x >> 5];
 
-	if (tid == 0) s_bc[0] = atomicAdd(&a.ctrl->ticket, 1u);
-	__syncthreads();
-	const uint32_t tile = s_bc[0];
-	if (tile >= a.n_tiles) return;
-	const uint64_t ts = (uint64_t)tile * ZK_TILE_BYTES;
-	uint64_t avail = a.nbytes_pad - ts;
-	const uint32_t wlen = avail < (uint64_t)(ZK_TILE_BYTES + ZK_TILE_OVERHANG)
-	    ? (uint32_t)avail : (ZK_TILE_BYTES + ZK_TILE_OVERHANG);
+	uint32_t chunk = 0;
+	if (lane == 0) chunk = atomicAdd(&a.ctrl->ticket, 1u);
+	chunk = __shfl_sync(0xffffffffu, chunk, 0);
+	if (chunk >= a.n_chunks) return;
+	const uint64_t cs = (uint64_t)chunk << ZK_CHUNK_LOG2;
+	const uint64_t avail = a.nbytes_pad - cs;
+	const uint32_t wlen = avail < (uint64_t)ZK_WIN ? (uint32_t)avail : ZK_WIN;
 
-	/* ---- stage the tile: 16-byte coalesced streaming loads ---- */
+	/* ---- stage the chunk: 16-byte coalesced streaming loads, 6 in flight per lane ---- */
 	{
-		const uint4 *src = reinterpret_cast<const uint4 *>(a.bytes + ts);
-		uint4 *dst = reinterpret_cast<uint4 *>(s_tile);
+		const uint4 *src = reinterpret_cast<const uint4 *>(a.bytes + cs);
+		uint4 *dst = reinterpret_cast<uint4 *>(c.tile);
 		const uint32_t nvec = wlen >> 4;
-		uint32_t i = tid;
-		for (; i + 3 * ZK_DECODE_THREADS < nvec; i += 4 * ZK_DECODE_THREADS) {
-			uint4 v0 = ld_stream16(src + i);
-			uint4 v1 = ld_stream16(src + i + ZK_DECODE_THREADS);
-			uint4 v2 = ld_stream16(src + i + 2 * ZK_DECODE_THREADS);
-			uint4 v3 = ld_stream16(src + i + 3 * ZK_DECODE_THREADS);
-			dst[i] = v0; dst[i + ZK_DECODE_THREADS] = v1;
-			dst[i + 2 * ZK_DECODE_THREADS] = v2; dst[i + 3 * ZK_DECODE_THREADS] = v3;
+		uint32_t i = lane;
+		for (; i + 5 * 32 < nvec; i += 6 * 32) {
+			uint4 v0 = ld_stream16(src + i), v1 = ld_stream16(src + i + 32), v2 = ld_stream16(src + i + 64);
+			uint4 v3 = ld_stream16(src + i + 96), v4 = ld_stream16(src + i + 128), v5 = ld_stream16(src + i + 160);
+			dst[i] = v0; dst[i + 32] = v1; dst[i + 64] = v2; dst[i + 96] = v3; dst[i + 128] = v4; dst[i + 160] = v5;
 		}
-		for (; i < nvec; i += ZK_DECODE_THREADS) dst[i] = ld_stream16(src + i);
+		for (; i < nvec; i += 32) dst[i] = ld_stream16(src + i);
+		if (lane == 0) *reinterpret_cast<uint4 *>(c.tile + (nvec << 4)) = make_uint4(0, 0, 0, 0);
+		for (uint32_t w = lane; w < ZK_BMW; w += 32) {
+			c.m_buf[w] = 0; c.m_acl[w] = 0; c.m_stat[w] = 0; c.sub0[w] = 0; c.sub1[w] = 0; c.fstart[w] = 0;
+		}
 	}
 	Rd rd;
-	rd.sm = s_tile; rd.lo = ts; rd.wlen = wlen; rd.g = a.bytes;
+	rd.sm = c.tile; rd.lo = cs; rd.wlen = wlen; rd.g = a.bytes;
 
-	const uint32_t g0 = (uint32_t)(ts >> a.glog2);
-	const uint32_t g1 = g0 + (ZK_TILE_BYTES >> a.glog2);
+	const uint32_t gsh = ZK_CHUNK_LOG2 - a.glog2;
+	const uint32_t g0 = chunk << gsh, g1 = (chunk + 1) << gsh;
 	const uint32_t f0 = a.g_base[g0];
 	const uint32_t f1 = (g1 < a.n_gran) ? a.g_base[g1] : (uint32_t)a.n_frames;
 	const uint32_t nfr = f1 - f0;
-	const bool single = nfr <= ZK_DECODE_THREADS;
-	__syncthreads();
+	__syncwarp();
 
-	/* ---- pass 1: parse, write FRAMES columns, count side rows ---- */
-	Parsed p;
-	uint64_t foff = 0; int32_t flen = 0;
-	uint32_t ex0 = 0, ex1 = 0, ex2 = 0;
-	uint32_t tile_tot[3] = { 0, 0, 0 };
-	for (uint32_t r0 = 0; r0 < nfr || r0 == 0; r0 += ZK_DECODE_THREADS) {
-		const uint32_t k = r0 + tid;
-		const bool valid = k < nfr;
-		p.n_stat = p.n_buf = p.n_acl = 0;
-		if (valid) {
-			const uint32_t f = f0 + k;
-			foff = a.o.frame_off[f];
-			flen = a.o.frame_len[f];
-			const uint32_t s = a.o.session[f];
-			parse_frame(rd, a, foff, flen, s, f - __ldg(a.o.sess_first_frame + s), p);
-			a.o.meta[f] = p.meta;
-			a.o.xid[f] = p.xid;
-			a.o.zxid[f] = p.zxid;
-			a.o.err[f] = p.err;
-			a.o.a0[f] = p.a0;
-			a.o.a1[f] = p.a1;
-		}
-		uint32_t t[3];
-		block_scan3(p.n_stat, p.n_buf, p.n_acl, ex0, ex1, ex2, t, s_w);
-		tile_tot[0] += t[0]; tile_tot[1] += t[1]; tile_tot[2] += t[2];
-		if (nfr == 0) break;
-	}
-
-	/* ---- decoupled look-back over tiles: exclusive prefix of (stat, buf, acl) rows ---- */
-	if (tid < 32) {
-		uint32_t e0 = 0, e1 = 0, e2 = 0;
-		if (tile > 0) {
-			if (tid == 0) {
-				a.lb_agg[tile * 4 + 0] = tile_tot[0];
-				a.lb_agg[tile * 4 + 1] = tile_tot[1];
-				a.lb_agg[tile * 4 + 2] = tile_tot[2];
-				st_release(a.lb_flag + tile, ZK_LB_AGG);
-			}
-			int64_t j = (int64_t)tile - 1;
-			uint32_t spins = 0;
-			for (;;) {
-				const int64_t idx = j - (int64_t)tid;
-				uint32_t st = ZK_LB_PFX;
-				if (idx >= 0) st = ld_acquire(a.lb_flag + idx);
-				if (__any_sync(0xffffffffu, st == ZK_LB_EMPTY)) {
-					if (++spins > ZK_SPIN_LIMIT) {
-						if (tid == 0) atomicOr(&a.ctrl->error, ZK_DERR_LOOKBACK);
-						break;
-					}
-					__nanosleep(64);
-					continue;
-				}
-				const uint32_t pm = __ballot_sync(0xffffffffu, st == ZK_LB_PFX);
-				const int first = __ffs(pm) - 1;   /* nearest predecessor holding a full prefix */
-				uint32_t c0 = 0, c1 = 0, c2 = 0;
-				if (idx >= 0 && (first < 0 || (int)tid <= first)) {
-					const uint32_t *src = (first >= 0 && (int)tid == first) ? a.lb_pfx : a.lb_agg;
-					c0 = __ldcg(src + idx * 4 + 0);
-					c1 = __ldcg(src + idx * 4 + 1);
-					c2 = __ldcg(src + idx * 4 + 2);
-				}
-				for (int d = 16; d > 0; d >>= 1) {
-					c0 += __shfl_xor_sync(0xffffffffu, c0, d);
-					c1 += __shfl_xor_sync(0xffffffffu, c1, d);
-					c2 += __shfl_xor_sync(0xffffffffu, c2, d);
-				}
-				e0 += c0; e1 += c1; e2 += c2;
-				if (first >= 0) break;
-				j -= 32;
+	/* ---- frames: lane k handles frames f0+k, f0+k+32, ... ---- */
+	Parsed lp;                       /* the chunk's long frame (reaches past the tile), if this lane has it */
+	uint64_t l_foff = 0; int32_t l_flen = 0; uint32_t l_f = 0;
+	lp.n_stat = lp.n_buf = lp.n_acl = 0;
+	uint32_t n_slow = 0;
+	for (uint32_t k0 = 0; k0 < nfr; k0 += 32) {
+		const uint32_t k = k0 + lane;
+		if (k >= nfr) continue;
+		const uint32_t f = f0 + k;
+		const uint64_t foff = a.o.frame_off[f];
+		const int32_t flen = a.o.frame_len[f];
+		const uint32_t s = a.o.session[f];
+		const uint32_t rel = (uint32_t)(foff - cs);
+		atomicOr(&c.fstart[rel >> 7], 1u << ((rel >> 2) & 31));
+		const bool inwin = rel + 4u + (uint32_t)flen <= wlen;
+		const bool server = a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER);
+		const uint32_t hs = a.sess_hs ? __ldg(a.sess_hs + s) : 1u;
+		const uint32_t idx = f - __ldg(a.o.sess_first_frame + s);
+		FrameCols o;
+		int done = -1;
+		if (inwin && idx >= hs) {
+			if (server) {
+				done = fast_request<FAST_MARK>(c, rel + 4, (uint32_t)flen, o);
+				if (done == 0) fast_request<FAST_UNMARK>(c, rel + 4, (uint32_t)flen, o);
+			} else {
+				done = fast_response<FAST_MARK>(c, a, rel + 4, (uint32_t)flen, s, o);
+				if (done == 0) fast_response<FAST_UNMARK>(c, a, rel + 4, (uint32_t)flen, s, o);
 			}
 		}
-		if (tid == 0) {
-			a.lb_pfx[tile * 4 + 0] = e0 + tile_tot[0];
-			a.lb_pfx[tile * 4 + 1] = e1 + tile_tot[1];
-			a.lb_pfx[tile * 4 + 2] = e2 + tile_tot[2];
-			st_release(a.lb_flag + tile, ZK_LB_PFX);
-			s_bc[1] = e0; s_bc[2] = e1; s_bc[3] = e2;
-			if (tile == a.n_tiles - 1) {
-				a.ctrl->n_stat = (unsigned long long)e0 + tile_tot[0];
-				a.ctrl->n_buf = (unsigned long long)e1 + tile_tot[1];
-				a.ctrl->n_acl = (unsigned long long)e2 + tile_tot[2];
+		if (done != 1) {
+			Parsed p;
+			n_slow++;
+			parse_frame(rd, a, foff, flen, s, idx, p);
+			o.meta = p.meta; o.xid = p.xid; o.zxid = p.zxid; o.err = p.err; o.a0 = p.a0; o.a1 = p.a1;
+			if (p.n_stat | p.n_buf | p.n_acl) {
+				if (inwin) {
+					mark_from_parsed(c, rd, rel + 4, foff + 4, flen, p);
+				} else {
+					lp = p; l_foff = foff; l_flen = flen; l_f = f;
+				}
+			}
+		}
+		a.o.meta[f] = o.meta;
+		a.o.xid[f] = o.xid;
+		a.o.zxid[f] = o.zxid;
+		a.o.err[f] = o.err;
+		a.o.a0[f] = o.a0;
+		a.o.a1[f] = o.a1;
+	}
+	__syncwarp();
+	n_slow = warp_sum(n_slow);
+	if (lane == 0 && n_slow) atomicAdd(&a.ctrl->n_slow, (unsigned long long)n_slow);
+
+	/* ---- row counts of this chunk; prefix of frame-start bits per bitmap word ---- */
+	uint32_t nb = 0, na = 0, ns = 0;
+	{
+		uint32_t run = 0;
+		for (uint32_t w0 = 0; w0 < ZK_BMW; w0 += 32) {
+			const uint32_t w = w0 + lane;
+			uint32_t fc = 0;
+			if (w < ZK_BMW) {
+				nb += __popc(c.m_buf[w]); na += __popc(c.m_acl[w]); ns += __popc(c.m_stat[w]);
+				fc = __popc(c.fstart[w]);
+			}
+			const uint32_t inc = warp_incl_scan(fc, lane);
+			if (w < ZK_BMW) c.fpre[w] = (uint16_t)(run + inc - fc);
+			run += __shfl_sync(0xffffffffu, inc, 31);
+		}
+	}
+	nb = warp_sum(nb); na = warp_sum(na); ns = warp_sum(ns);
+	const uint32_t tb = nb + warp_sum(lp.n_buf), ta = na + warp_sum(lp.n_acl), ts = ns + warp_sum(lp.n_stat);
+	__syncwarp();
+
+	/* ---- decoupled look-back over chunks: exclusive prefix of (stat, buf, acl) rows.
+	 * A chunk's descriptor is one aligned 16-byte word { state, stat, buf, acl } written and
+	 * read with single 128-bit accesses, so state and counts always belong together: first
+	 * the chunk's own totals (AGG), later its inclusive prefix (PFX). ---- */
+	uint32_t e0 = 0, e1 = 0, e2 = 0;
+	if (chunk > 0) {
+		if (lane == 0) st_desc(a.lb + chunk, make_uint4(ZK_LB_AGG, ts, tb, ta));
+		int64_t j = (int64_t)chunk - 1;
+		uint32_t spins = 0, ns_sleep = 16;
+		for (;;) {
+			const int64_t idx = j - (int64_t)lane;
+			uint4 d = make_uint4(ZK_LB_PFX, 0, 0, 0);
+			if (idx >= 0) d = ld_desc(a.lb + idx);
+			if (__any_sync(0xffffffffu, d.x == ZK_LB_EMPTY)) {
+				if (++spins > ZK_SPIN_LIMIT) {
+					if (lane == 0) atomicOr(&a.ctrl->error, ZK_DERR_LOOKBACK);
+					break;
+				}
+				__nanosleep(ns_sleep);
+				if (ns_sleep < 512) ns_sleep <<= 1;
+				continue;
+			}
+			const uint32_t pm = __ballot_sync(0xffffffffu, d.x == ZK_LB_PFX);
+			const int first = __ffs(pm) - 1;   /* nearest predecessor holding a full prefix */
+			const bool use = (first < 0 || (int)lane <= first);
+			e0 += warp_sum(use ? d.y : 0u);
+			e1 += warp_sum(use ? d.z : 0u);
+			e2 += warp_sum(use ? d.w : 0u);
+			if (first >= 0) break;
+			j -= 32;
+		}
+	}
+	if (lane == 0) {
+		st_desc(a.lb + chunk, make_uint4(ZK_LB_PFX, e0 + ts, e1 + tb, e2 + ta));
+		if (chunk == a.n_chunks - 1) {
+			a.ctrl->n_stat = (unsigned long long)e0 + ts;
+			a.ctrl->n_buf = (unsigned long long)e1 + tb;
+			a.ctrl->n_acl = (unsigned long long)e2 + ta;
+		}
+	}
+	if (ts + tb + ta == 0) return;
+
+	/* ---- emit: compact each bitmap, lane w owns bitmap word w (128 input bytes) ---- */
+	const zkb_decoded &o = a.o;
+	if (nb) {
+		uint32_t run = e1;
+		for (uint32_t w0 = 0; w0 < ZK_BMW; w0 += 32) {
+			const uint32_t w = w0 + lane;
+			uint32_t bits = (w < ZK_BMW) ? c.m_buf[w] : 0u;
+			const uint32_t cnt = __popc(bits);
+			const uint32_t inc = warp_incl_scan(cnt, lane);
+			uint32_t row = run + inc - cnt;
+			run += __shfl_sync(0xffffffffu, inc, 31);
+			while (bits) {
+				const uint32_t b = __ffs(bits) - 1;
+				bits &= bits - 1;
+				const uint32_t prel = ((w * 32 + b) << 2) | ((c.sub0[w] >> b) & 1) | (((c.sub1[w] >> b) & 1) << 1);
+				const int32_t len = (int32_t)sm_be32(c.tile, prel);
+				const uint32_t owner = f0 + c.fpre[w] + __popc(c.fstart[w] & ((1u << b) - 1)) - 1;
+				if (row < o.cap_buf) {
+					o.buf_frame[row] = owner;
+					o.buf_off[row] = cs + prel + 4;
+					o.buf_len[row] = len > 0 ? len : 0;
+				}
+				row++;
 			}
 		}
 	}
-	__syncthreads();
-	uint32_t run0 = s_bc[1], run1 = s_bc[2], run2 = s_bc[3];
-	if (tile_tot[0] + tile_tot[1] + tile_tot[2] == 0) return;
-
-	/* ---- pass 2: side rows ---- */
-	if (single) {
-		if (tid < nfr && (p.n_stat | p.n_buf | p.n_acl))
-			emit_side(rd, a, foff, flen, p, f0 + tid, run0 + ex0, run1 + ex1, run2 + ex2);
-		return;
-	}
-	for (uint32_t r0 = 0; r0 < nfr; r0 += ZK_DECODE_THREADS) {
-		const uint32_t k = r0 + tid;
-		const bool valid = k < nfr;
-		p.n_stat = p.n_buf = p.n_acl = 0;
-		if (valid) {
-			const uint32_t f = f0 + k;
-			foff = a.o.frame_off[f];
-			flen = a.o.frame_len[f];
-			const uint32_t s = a.o.session[f];
-			parse_frame(rd, a, foff, flen, s, f - __ldg(a.o.sess_first_frame + s), p);
+	if (na) {
+		uint32_t run = e2;
+		for (uint32_t w0 = 0; w0 < ZK_BMW; w0 += 32) {
+			const uint32_t w = w0 + lane;
+			uint32_t bits = (w < ZK_BMW) ? c.m_acl[w] : 0u;
+			const uint32_t cnt = __popc(bits);
+			const uint32_t inc = warp_incl_scan(cnt, lane);
+			uint32_t row = run + inc - cnt;
+			run += __shfl_sync(0xffffffffu, inc, 31);
+			while (bits) {
+				const uint32_t b = __ffs(bits) - 1;
+				bits &= bits - 1;
+				const uint32_t prel = ((w * 32 + b) << 2) | ((c.sub0[w] >> b) & 1) | (((c.sub1[w] >> b) & 1) << 1);
+				const uint32_t owner = f0 + c.fpre[w] + __popc(c.fstart[w] & ((1u << b) - 1)) - 1;
+				if (row < o.cap_acl) {
+					o.acl_frame[row] = owner;
+					o.acl_perms[row] = (int32_t)sm_be32(c.tile, prel);
+				}
+				row++;
+			}
 		}
-		uint32_t t[3];
-		block_scan3(p.n_stat, p.n_buf, p.n_acl, ex0, ex1, ex2, t, s_w);
-		if (valid && (p.n_stat | p.n_buf | p.n_acl))
-			emit_side(rd, a, foff, flen, p, f0 + k, run0 + ex0, run1 + ex1, run2 + ex2);
-		run0 += t[0]; run1 += t[1]; run2 += t[2];
 	}
+	if (ns) {
+		uint32_t run = e0;
+		for (uint32_t w0 = 0; w0 < ZK_BMW; w0 += 32) {
+			const uint32_t w = w0 + lane;
+			uint32_t bits = (w < ZK_BMW) ? c.m_stat[w] : 0u;
+			const uint32_t cnt = __popc(bits);
+			const uint32_t inc = warp_incl_scan(cnt, lane);
+			uint32_t row = run + inc - cnt;
+			run += __shfl_sync(0xffffffffu, inc, 31);
+			while (bits) {
+				const uint32_t b = __ffs(bits) - 1;
+				bits &= bits - 1;
+				const uint32_t q = ((w * 32 + b) << 2) | ((c.sub0[w] >> b) & 1) | (((c.sub1[w] >> b) & 1) << 1);
+				const uint32_t owner = f0 + c.fpre[w] + __popc(c.fstart[w] & ((1u << b) - 1)) - 1;
+				if (row < o.cap_stat) {
+					/* 68 bytes = 17 big-endian words from 18 aligned shared-memory words */
+					const uint32_t *wp = reinterpret_cast<const uint32_t *>(c.tile + (q & ~3u));
+					const uint32_t sh = (q & 3u) * 8;
+					uint32_t x[18];
+#pragma unroll
+					for (int i = 0; i < 18; ++i) x[i] = wp[i];
+					uint32_t v[17];
+#pragma unroll
+					for (int i = 0; i < 17; ++i) v[i] = bswap32(__funnelshift_r(x[i], x[i + 1], sh));
+#define Q64(i) ((int64_t)(((uint64_t)v[i] << 32) | (uint64_t)v[(i) + 1]))
+					o.stat_frame[row] = owner;
+					o.czxid[row] = Q64(0); o.mzxid[row] = Q64(2); o.ctime[row] = Q64(4); o.mtime[row] = Q64(6);
+					o.version[row] = (int32_t)v[8]; o.cversion[row] = (int32_t)v[9]; o.aversion[row] = (int32_t)v[10];
+					o.ephemeralOwner[row] = Q64(11);
+					o.dataLength[row] = (int32_t)v[13]; o.numChildren[row] = (int32_t)v[14];
+					o.pzxid[row] = Q64(15);
+#undef Q64
+				}
+				row++;
+			}
+		}
+	}
+	/* the long frame's rows come last: it is the chunk's last frame */
+	if (lp.n_stat | lp.n_buf | lp.n_acl)
+		emit_side(rd, a, l_foff, l_flen, lp, l_f, e0 + ns, e1 + nb, e2 + na);
 }
 
 /* ================================================================================== */
@@ -1019,8 +1530,8 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 }
 
 struct ScratchLayout {
-	size_t g_assumed, g_out, g_carry, g_cnt, g_base, g_dirty, blk, lb_flag, lb_agg, lb_pfx, total;
-	uint32_t glog2, n_gran, n_tiles, n_blk;
+	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, blk, lb, total;
+	uint32_t glog2, n_gran, n_chunks, n_blk;
 };
 
 static ScratchLayout zk_layout(uint64_t nbytes)
@@ -1029,19 +1540,19 @@ static ScratchLayout zk_layout(uint64_t nbytes)
 	memset(&L, 0, sizeof (L));
 	L.glog2 = zk_pick_glog2(nbytes);
 	L.n_gran = (uint32_t)((nbytes + (1ull << L.glog2) - 1) >> L.glog2);
-	L.n_tiles = (uint32_t)((nbytes + ZK_TILE_BYTES - 1) / ZK_TILE_BYTES);
+	L.n_chunks = (uint32_t)((nbytes + ZK_CHUNK - 1) >> ZK_CHUNK_LOG2);
 	L.n_blk = (L.n_gran + SCAN_THREADS - 1) / SCAN_THREADS;
 	size_t o = 0;
-	L.g_assumed = o; o += zk_align_up((size_t)L.n_gran * 8, 256);
-	L.g_out = o;     o += zk_align_up((size_t)L.n_gran * 8, 256);
+	L.g_assumed = o; o += zk_align_up((size_t)L.n_gran * 16, 256);
+	L.g_out = o;     o += zk_align_up((size_t)L.n_gran * 16, 256);
 	L.g_carry = o;   o += zk_align_up((size_t)L.n_gran * 8, 256);
-	L.g_cnt = o;     o += zk_align_up((size_t)L.n_gran * 4, 256);
+	L.g_cnt = o;     o += zk_align_up((size_t)L.n_gran * 8, 256);
+	L.g_sel = o;     o += zk_align_up((size_t)L.n_gran, 256);
 	L.g_base = o;    o += zk_align_up((size_t)(L.n_gran + 1) * 4, 256);
 	L.g_dirty = o;   o += zk_align_up((size_t)L.n_gran, 256);
+	L.g_src = o;     o += zk_align_up((size_t)L.n_gran * 4, 256);
 	L.blk = o;       o += zk_align_up((size_t)(L.n_blk + 1) * sizeof (ScanVal), 256);
-	L.lb_flag = o;   o += zk_align_up((size_t)L.n_tiles * 4, 256);
-	L.lb_agg = o;    o += zk_align_up((size_t)L.n_tiles * 16, 256);
-	L.lb_pfx = o;    o += zk_align_up((size_t)L.n_tiles * 16, 256);
+	L.lb = o;        o += zk_align_up((size_t)L.n_chunks * 16, 256);
 	L.total = o;
 	return L;
 }
@@ -1076,6 +1587,7 @@ static int zk_fill_split_args(zkb_ctx *ctx, SplitArgs &sa, const ScratchLayout &
 	sa.g_assumed = (uint64_t *)(S + L.g_assumed); sa.g_out = (uint64_t *)(S + L.g_out);
 	sa.g_carry = (uint64_t *)(S + L.g_carry); sa.g_cnt = (uint32_t *)(S + L.g_cnt);
 	sa.g_base = (uint32_t *)(S + L.g_base); sa.g_dirty = (uint8_t *)(S + L.g_dirty);
+	sa.g_src = (uint32_t *)(S + L.g_src); sa.g_sel = (uint8_t *)(S + L.g_sel);
 	if (out) {
 		sa.frame_off = out->frame_off; sa.frame_len = out->frame_len; sa.session = out->session;
 		sa.cap_frames = out->cap_frames;
@@ -1125,6 +1637,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	ScanVal *blk = (ScanVal *)((uint8_t *)ctx->d_scratch + L.blk);
 
 	const uint32_t split_blocks = (L.n_gran + 127) / 128;
+	ZK_EV(ctx, 0);
 	k_split<MODE_SPEC><<<split_blocks, 128, 0, ctx->stream>>>(sa);
 	LAUNCH_CHECK(ctx);
 	for (uint32_t iter = 0;; ++iter) {
@@ -1134,6 +1647,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		LAUNCH_CHECK(ctx);
 		k_scan_apply<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk);
 		LAUNCH_CHECK(ctx);
+		ZK_EV(ctx, 1);
 		if ((rc = zk_read_ctrl(ctx))) return rc;
 		if (ctx->h_ctrl->error & ZK_DERR_SESSIONS) {
 			snprintf(ctx->err, sizeof (ctx->err), "zkb_decode: session offsets invalid");
@@ -1145,9 +1659,12 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 			return ZKB_EINTERNAL;
 		}
 		ctx->split_fixups++;
-		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_dirty, 0, sizeof (unsigned int), ctx->stream));
-		k_split<MODE_FIX><<<split_blocks, 128, 0, ctx->stream>>>(sa);
-		LAUNCH_CHECK(ctx);
+		const bool rewalk = ctx->h_ctrl->n_rewalk != 0;
+		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_dirty, 0, 2 * sizeof (unsigned int), ctx->stream));
+		if (rewalk) {
+			k_split<MODE_FIX><<<split_blocks, 128, 0, ctx->stream>>>(sa);
+			LAUNCH_CHECK(ctx);
+		}
 	}
 	*n_frames = ctx->h_ctrl->n_frames;
 	return ZKB_OK;
@@ -1180,8 +1697,11 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, out);
 	const uint32_t split_blocks = (L.n_gran + 127) / 128;
 	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->ticket, 0, sizeof (unsigned int), ctx->stream));
+	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long), ctx->stream));
+	ZK_EV(ctx, 2);
 	k_split<MODE_EMIT><<<split_blocks, 128, 0, ctx->stream>>>(sa);
 	LAUNCH_CHECK(ctx);
+	ZK_EV(ctx, 3);
 	/* sess_first_frame[nsess] = n_frames */
 	ZK_CUDA(ctx, cudaMemcpyAsync(out->sess_first_frame + nsess, &ctx->d_ctrl->n_frames, sizeof (uint32_t),
 	    cudaMemcpyDeviceToDevice, ctx->stream));
@@ -1193,18 +1713,25 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	if (xid && xid->ops) {
 		da.xt_base = xid->base; da.xt_count = xid->count; da.xt_off = xid->off; da.xt_ops = xid->ops;
 	}
-	da.g_base = sa.g_base; da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_tiles = L.n_tiles;
+	da.g_base = sa.g_base; da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_chunks = L.n_chunks;
 	da.n_frames = n_frames; da.o = *out;
-	da.lb_flag = (uint32_t *)(S + L.lb_flag); da.lb_agg = (uint32_t *)(S + L.lb_agg);
-	da.lb_pfx = (uint32_t *)(S + L.lb_pfx); da.ctrl = ctx->d_ctrl;
-	ZK_CUDA(ctx, cudaMemsetAsync(da.lb_flag, 0, (size_t)L.n_tiles * 4, ctx->stream));
-	k_decode<<<L.n_tiles, ZK_DECODE_THREADS, 0, ctx->stream>>>(da);
+	da.lb = (uint4 *)(S + L.lb); da.ctrl = ctx->d_ctrl;
+	ZK_CUDA(ctx, cudaMemsetAsync(da.lb, 0, (size_t)L.n_chunks * 16, ctx->stream));
+	ZK_EV(ctx, 4);
+	k_decode<<<(L.n_chunks + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
 	LAUNCH_CHECK(ctx);
+	ZK_EV(ctx, 5);
 	if ((rc = zk_read_ctrl(ctx))) return rc;
+	if (ctx->timing) {
+		cudaEventElapsedTime(&ctx->phase_ms[0], ctx->ev[0], ctx->ev[1]);
+		cudaEventElapsedTime(&ctx->phase_ms[1], ctx->ev[2], ctx->ev[3]);
+		cudaEventElapsedTime(&ctx->phase_ms[2], ctx->ev[4], ctx->ev[5]);
+	}
 	if (ctx->h_ctrl->error) {
 		snprintf(ctx->err, sizeof (ctx->err), "zkb_decode: device error bits 0x%x", ctx->h_ctrl->error);
 		return ZKB_EINTERNAL;
 	}
+	ctx->slow_frames = ctx->h_ctrl->n_slow;
 	out->n_stat = ctx->h_ctrl->n_stat;
 	out->n_buf = ctx->h_ctrl->n_buf;
 	out->n_acl = ctx->h_ctrl->n_acl;

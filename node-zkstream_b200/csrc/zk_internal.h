@@ -13,12 +13,8 @@
 #include "../../include/zkbatch.h"
 
 /* ---- geometry ---------------------------------------------------------------------- */
-#define ZK_TILE_BYTES     32768u  /* bytes of input one decode CTA stages in shared memory */
-#define ZK_TILE_OVERHANG   2048u  /* extra bytes staged so frames that start near the end of a
-                                     tile are still read from shared memory */
-#define ZK_DECODE_THREADS   256
-#define ZK_GRAN_MIN_LOG2     10   /* splitter granule: 1 KiB .. 32 KiB (<= tile) */
-#define ZK_GRAN_MAX_LOG2     15
+#define ZK_GRAN_MIN_LOG2     10   /* splitter granule: 1 KiB .. 8 KiB (= one decode chunk) */
+#define ZK_GRAN_MAX_LOG2     13
 #define ZK_MAX_BATCH_BYTES ((1ull << 34) - 1)  /* keeps every row index below 2^32 */
 
 #define ZK_NONE     0xFFFFFFFFFFFFFFFFull  /* no live chain */
@@ -36,12 +32,13 @@
 
 struct zk_ctrl {
 	unsigned int       error;
-	unsigned int       n_dirty;
+	unsigned int       n_dirty;     /* granules whose state changed in the last scan (dirty or re-selected) */
 	unsigned int       ticket;
-	unsigned int       pad0;
+	unsigned int       n_rewalk;    /* of those, granules that need a new walk */
 	unsigned long long n_frames;
 	unsigned long long n_stat, n_buf, n_acl;
 	unsigned long long enc_bytes;
+	unsigned long long n_slow;   /* frames that needed the generic (exact) parser */
 };
 
 struct zkb_ctx {
@@ -50,6 +47,7 @@ struct zkb_ctx {
 	char          err[512];
 	uint64_t      launches;
 	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
+	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
 	/* device scratch (grown on demand, never shrunk) */
 	void         *d_scratch;   size_t d_scratch_bytes;
 	zk_ctrl      *d_ctrl;
@@ -60,7 +58,14 @@ struct zkb_ctx {
 	void         *h_out;       size_t h_out_bytes;     /* pinned mirror of d_out */
 	void         *h_in;        size_t h_in_bytes;      /* pinned bounce buffer for small arrays */
 	int           sm_count;
+	/* optional per-phase CUDA-event timing (zkb_ctx_set_timing) */
+	int           timing;
+	cudaEvent_t   ev[6];          /* split begin/end, emit begin/end, decode begin/end */
+	float         phase_ms[3];    /* split, emit, decode of the last decode call */
 };
+
+#define ZK_EV(ctx, i)                                                                    \
+	do { if ((ctx)->timing) cudaEventRecord((ctx)->ev[i], (ctx)->stream); } while (0)
 
 #define ZK_CUDA(ctx, call)                                                              \
 	do {                                                                                \

@@ -335,3 +335,78 @@ def fuzz_corpus(seed, nsessions=24, max_frames=40, p_mutate=0.3, p_tail=0.3, p_b
             tail = full[:rng.randrange(1, len(full))]
         c.add(b"".join(parts) + tail, server=server, hs=hs, xidmap=xm)
     return c
+
+
+# ---- benchmark-scale corpora from the C generator (csrc/zkgen.c) --------------------------
+
+_gen = None
+
+
+def _genlib():
+    global _gen
+    if _gen is None:
+        import ctypes as C
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libzkgen.so")
+        if not os.path.exists(path):
+            raise ImportError("%s is missing: run `python node-zkstream_b200/build.py`" % path)
+        g = C.CDLL(path)
+        P = C.c_void_p
+        g.zkgen_cfg2_sizes.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, P, P, C.c_int]
+        g.zkgen_cfg2_fill.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, P, P, P, P, P, C.c_int]
+        g.zkgen_cfg1.restype = C.c_uint64
+        g.zkgen_cfg1.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, P]
+        g.zkgen_cfg3.restype = C.c_uint64
+        g.zkgen_cfg3.argtypes = [C.c_uint64, C.c_uint64, P]
+        _gen = g
+    return _gen
+
+
+class PairedCorpus:
+    """Config-2 replay: `req`/`rsp` byte arrays with per-session offsets, and the dense xid table
+    (`ops`, [nsessions * frames] wire opcodes, OP_NONE past each session's last xid)."""
+
+    def __init__(self, nsessions, frames):
+        self.nsessions, self.frames = nsessions, frames
+
+    def xidtable(self):
+        from ._lib import XidTable
+        n = self.nsessions
+        return XidTable(np.zeros(n, np.int32), np.full(n, self.frames, np.uint32), self.ops)
+
+
+def native_cfg2(seed, nsessions, frames, nthreads=None, alloc=None):
+    """Paired request/response replay (config 2) from the C generator.  `alloc(nbytes)` may
+    return a writable uint8 array to fill (e.g. pinned memory); default is numpy."""
+    import os
+    g = _genlib()
+    nthreads = nthreads or os.cpu_count() or 1
+    alloc = alloc or (lambda n: np.empty(n, dtype=np.uint8))
+    pc = PairedCorpus(nsessions, frames)
+    pc.req_off = np.zeros(nsessions + 1, dtype=np.uint64)
+    pc.rsp_off = np.zeros(nsessions + 1, dtype=np.uint64)
+    g.zkgen_cfg2_sizes(seed, nsessions, frames, pc.req_off.ctypes.data, pc.rsp_off.ctypes.data, nthreads)
+    pc.req = alloc(int(pc.req_off[-1]))
+    pc.rsp = alloc(int(pc.rsp_off[-1]))
+    pc.ops = np.full(nsessions * frames, _abi.OP_NONE, dtype=np.int8)
+    g.zkgen_cfg2_fill(seed, nsessions, frames, pc.req_off.ctypes.data, pc.rsp_off.ctypes.data,
+                      pc.req.ctypes.data, pc.rsp.ctypes.data, pc.ops.ctypes.data, nthreads)
+    pc.req_flags = np.full(nsessions, _abi.SESS_SERVER, dtype=np.uint8)
+    pc.rsp_flags = np.zeros(nsessions, dtype=np.uint8)
+    return pc
+
+
+def native_cfg1(seed, n, payload=256):
+    g = _genlib()
+    size = g.zkgen_cfg1(seed, n, payload, None)
+    out = np.empty(size, dtype=np.uint8)
+    g.zkgen_cfg1(seed, n, payload, out.ctypes.data)
+    return out
+
+
+def native_cfg3(seed, n):
+    g = _genlib()
+    size = g.zkgen_cfg3(seed, n, None)
+    out = np.empty(size, dtype=np.uint8)
+    g.zkgen_cfg3(seed, n, out.ctypes.data)
+    return out
