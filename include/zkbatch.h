@@ -334,6 +334,33 @@ int zkb_xidtab_build_host(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessio
 int zkb_xidtab_build_dev(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessions,
     const zkb_xidtab *layout, int8_t *ops_out);
 
+/*
+ * The same table build for callers that must not allocate.  (No counterpart in the
+ * reference: it exists for the embedding, not for the protocol.)  Who needs it: a host
+ * whose own pool already owns all device memory, where a cudaMalloc made behind its back
+ * fails or fragments the pool; and a service loop that may not call cudaMalloc/cudaFree
+ * at all because those calls stall every stream on the device.  This entry point takes no
+ * context and calls no allocator: the per-xid scratch it needs is a fixed array inside the
+ * library image, ZKB_NOALLOC_MAX_XIDS slots of 8 bytes (8 MiB), present on every GPU that
+ * has loaded the library for as long as the process lives.
+ *
+ * All pointers — the req columns (meta, frame_len, session, xid), the layout arrays and
+ * ops_out — are DEVICE pointers on the current device; `stream` is a cudaStream_t (NULL =
+ * the default stream) on which the work is queued, and the call returns once it has
+ * finished.  Results are identical to zkb_xidtab_build_dev.
+ *   - layout->nops above ZKB_NOALLOC_MAX_XIDS is refused with ZKB_ERANGE (text in errbuf);
+ *     cover more xids by building the table for a few sessions per call.
+ *   - The first call on each GPU looks up where the array lives on that GPU; make that
+ *     first call outside any stream capture.
+ *   - Every call uses the same array (a call clears the slots it is about to use), so two
+ *     calls whose GPU work overlaps, from any threads or streams, corrupt each other: run
+ *     them one after the other.
+ * errbuf (may be NULL) receives a message when the result is not ZKB_OK.
+ */
+#define ZKB_NOALLOC_MAX_XIDS (1u << 20)
+int zkb_xidtab_build_noalloc(const zkb_decoded *req, uint32_t nsessions, const zkb_xidtab *layout,
+    int8_t *ops_out, void *stream, char *errbuf, size_t errcap);
+
 /* ---- encode ----------------------------------------------------------------------------- */
 
 /*

@@ -11,6 +11,7 @@ SESS_SERVER = 1
 NO_OFFSET = 0xFFFFFFFFFFFFFFFF
 ENC_CONNECT_REQUEST, ENC_CONNECT_RESPONSE = -100, -101
 ENC_OK, ENC_UNSUPPORTED = 0, 1
+NOALLOC_MAX_XIDS = 1 << 20
 
 FIELD_NAMES = [
     "NONE", "XID", "ZXID", "ERR", "OPCODE", "PATH", "DATA", "WATCH", "VERSION", "FLAGS",
@@ -81,6 +82,8 @@ SYMBOLS = [
     ("zkb_decode_host", C.c_int, [P, P, C.c_uint64, C.POINTER(Sessions), C.POINTER(XidTab), C.POINTER(Decoded)]),
     ("zkb_xidtab_build_host", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P]),
     ("zkb_xidtab_build_dev", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P]),
+    ("zkb_xidtab_build_noalloc", C.c_int, [C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P, P,
+                                           C.c_char_p, C.c_size_t]),
     ("zkb_encode_dev", C.c_int, [P, C.POINTER(Requests), P, C.c_uint64, P, P, C.POINTER(C.c_uint64)]),
     ("zkb_encode_host", C.c_int, [P, C.POINTER(Requests), C.POINTER(P), C.POINTER(P), C.POINTER(P),
                                    C.POINTER(C.c_uint64)]),

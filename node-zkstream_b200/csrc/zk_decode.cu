@@ -1776,3 +1776,83 @@ int zk_xidtab_build_device(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessi
 	ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	return ZKB_OK;
 }
+
+/* ================================================================================== */
+/* xid table build for callers that cannot allocate                                    */
+
+/*
+ * zkb_xidtab_build_dev borrows the context's scratch, which the context obtained with
+ * cudaMalloc.  Two kinds of user of this library cannot go down that road: a host
+ * process that has already given all device memory to its own pool (an inference server
+ * or a database engine embedding the codec: a later cudaMalloc fails there, or breaks up
+ * the pool), and a latency-bound service loop in which cudaMalloc/cudaFree are off limits
+ * because they stall every stream on the device.  For them this entry point keeps the
+ * one piece of scratch the build needs — a 64-bit slot per xid — in a fixed array that
+ * is part of the library image.  Each GPU that loads libzkbatch.so carries these
+ * ZKB_NOALLOC_MAX_XIDS * 8 bytes (8 MiB) until the process ends.
+ */
+static __device__ __align__(256) unsigned long long zk_noalloc_slots[ZKB_NOALLOC_MAX_XIDS];
+
+#define ZK_NOALLOC_MAX_DEVICES 64
+static unsigned long long *zk_noalloc_addr[ZK_NOALLOC_MAX_DEVICES];   /* device address per GPU, 0 = not looked up yet */
+
+static int zk_noalloc_fail(char *errbuf, size_t errcap, int rc, const char *what, cudaError_t e)
+{
+	if (errbuf && errcap) {
+		if (e != cudaSuccess) snprintf(errbuf, errcap, "zkb_xidtab_build_noalloc: %s: %s", what, cudaGetErrorString(e));
+		else snprintf(errbuf, errcap, "zkb_xidtab_build_noalloc: %s", what);
+	}
+	return rc;
+}
+
+extern "C" __attribute__((visibility("default")))
+int zkb_xidtab_build_noalloc(const zkb_decoded *req, uint32_t nsessions, const zkb_xidtab *layout,
+    int8_t *ops_out, void *stream, char *errbuf, size_t errcap)
+{
+	if (errbuf && errcap) errbuf[0] = 0;
+	if (!req || !layout) return zk_noalloc_fail(errbuf, errcap, ZKB_EINVAL, "NULL argument", cudaSuccess);
+	const uint64_t n = layout->nops;
+	if (n > ZKB_NOALLOC_MAX_XIDS) {
+		if (errbuf && errcap)
+			snprintf(errbuf, errcap, "zkb_xidtab_build_noalloc: table of %llu xids exceeds the fixed scratch of %u; "
+			    "split the sessions over several calls or use zkb_xidtab_build_dev",
+			    (unsigned long long)n, (unsigned)ZKB_NOALLOC_MAX_XIDS);
+		return ZKB_ERANGE;
+	}
+	if (n == 0) return ZKB_OK;
+	if (!ops_out) return zk_noalloc_fail(errbuf, errcap, ZKB_EINVAL, "NULL ops_out", cudaSuccess);
+
+	/* The array's name means something only to device code.  Seen from the host it is a
+	 * handle, so the first call on each GPU asks the runtime where the array really lives
+	 * on that GPU and remembers the answer. */
+	int dev = -1;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "cudaGetDevice", e);
+	if (dev < 0 || dev >= ZK_NOALLOC_MAX_DEVICES)
+		return zk_noalloc_fail(errbuf, errcap, ZKB_ERANGE, "device ordinal out of range", cudaSuccess);
+	unsigned long long *slots = __atomic_load_n(&zk_noalloc_addr[dev], __ATOMIC_ACQUIRE);
+	if (!slots) {
+		void *p = NULL;
+		e = cudaGetSymbolAddress(&p, zk_noalloc_slots);
+		if (e != cudaSuccess || !p) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "cudaGetSymbolAddress", e);
+		slots = (unsigned long long *)p;
+		__atomic_store_n(&zk_noalloc_addr[dev], slots, __ATOMIC_RELEASE);
+	}
+
+	cudaStream_t st = (cudaStream_t)stream;
+	/* the slots still hold the previous call's keys: the part this call uses starts from zero */
+	e = cudaMemsetAsync(slots, 0, n * sizeof (unsigned long long), st);
+	if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "cudaMemsetAsync", e);
+	if (req->n_frames) {
+		k_xid_scatter<<<(unsigned)((req->n_frames + 255) / 256), 256, 0, st>>>(*req, req->n_frames, nsessions,
+		    layout->base, layout->count, layout->off, slots);
+		e = cudaGetLastError();
+		if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "k_xid_scatter launch", e);
+	}
+	k_xid_finish<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(slots, n, ops_out);
+	e = cudaGetLastError();
+	if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "k_xid_finish launch", e);
+	e = cudaStreamSynchronize(st);
+	if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "cudaStreamSynchronize", e);
+	return ZKB_OK;
+}
