@@ -9,5 +9,12 @@ package: without the built library and a CUDA device every call raises.
 from . import _abi, consts
 from ._lib import Context, XidTable, ZKBatchError, load, LIB_PATH
 from .columns import Columns
+from .errors import ZKProtocolError, ZKError
+from .materialise import LongDate, Materialiser
+from .encode import RequestBatch
+from .streams import ZKDecodeStream, ZKEncodeStream
+from .zkbuffer import JuteBuffer, ZKBuffer
 
-__all__ = ["Context", "XidTable", "ZKBatchError", "Columns", "load", "LIB_PATH", "consts"]
+__all__ = ["Context", "XidTable", "ZKBatchError", "Columns", "load", "LIB_PATH", "consts",
+           "ZKProtocolError", "ZKError", "LongDate", "Materialiser", "RequestBatch",
+           "ZKDecodeStream", "ZKEncodeStream", "JuteBuffer", "ZKBuffer"]

@@ -1,0 +1,90 @@
+"""The JavaScript half of the drop-in (node-zkstream_b200/js/materialise.js) against the
+reference, in the same JavaScript engine: columns from the CPU oracle are handed to the shim,
+which must rebuild exactly the packet objects (and error objects) that the reference's
+ZKDecodeStream produced for the same bytes (tests/golden/ref_decode.json).  Needs the
+SpiderMonkey shell built from the reference tree; skipped where that is absent."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import ref_js
+from _canon import _decanon_guard  # noqa: F401  (import check below)
+
+pytestmark = pytest.mark.skipif(not ref_js.available(), reason="reference JS engine not available here")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def js_array(a):
+    return "[" + ",".join(str(int(x)) for x in a) + "]"
+
+
+def js_array64(a):
+    """64-bit column -> interleaved [lo, hi] int32 words, as an Int32Array view would show it."""
+    w = np.ascontiguousarray(a).view(np.int32)
+    return js_array(w)
+
+
+def test_js_materialiser_reproduces_reference_packets(oracle, synth, zk):
+    from _canon import canon_events
+    g = json.load(open(os.path.join(GOLD, "ref_decode.json")))
+    sessions = [s for s in g["sessions"] if s["corpus"] in ("capture1+nasty", "fuzz0", "fuzz1", "fuzz2", "cfg2", "cfg3")]
+    c = synth.Corpus()
+    for s in sessions:
+        c.add(bytes.fromhex(s["hex"]), server=s["isServer"], hs=s["hs"], xidmap={int(k): v for k, v in s["xidMap"].items()})
+    d, off, fl, hs = c.arrays()
+    cols = oracle.decode(d, off, fl, hs, c.xidtable())
+    parts = ["var cols = {"]
+    for name, dt in zk._abi.FRAME_COLS + zk._abi.STAT_COLS + zk._abi.BUF_COLS + zk._abi.ACL_COLS + zk._abi.SESS_COLS:
+        a = getattr(cols, name)
+        parts.append("%s: %s," % (name, js_array64(a) if dt in ("i8", "u8") else js_array(a)))
+    parts.append("n_frames: %d, n_stat: %d, n_buf: %d, n_acl: %d};" % (cols.n_frames, cols.n_stat, cols.n_buf, cols.n_acl))
+    parts.append("var data = hex(%s);" % json.dumps(c.data.hex()))
+    parts.append(open(os.path.join(ROOT, "node-zkstream_b200", "js", "materialise.js")).read())
+    parts.append(r"""
+var jute = requireShim('./jute-buffer');
+var LongDate = (new jute.JuteBuffer({ buffer: new Buffer(8) })).readLongDate().constructor;
+var M = makeMaterialiser({ consts: requireShim('./zk-consts'), LongDate: LongDate,
+    ZKProtocolError: requireShim('./errors').ZKProtocolError, Buffer: Buffer });
+var m = new M(cols, data);
+for (var s = 0; s < %d; ++s) {
+	var out = [];
+	m.forEach(s, function (pkt) { out.push('{"pkt":' + canon(pkt) + '}'); },
+	    function (e) { out.push('{"error":{"code":' + jstr(e.code) + ',"message":' + jstr(e.message) + '}}'); });
+	print('{"events":[' + out.join(',') + ']}');
+}
+""" % len(sessions))
+    out = ref_js.run_js("\n".join(parts))
+    lines = [l for l in out.splitlines() if l.strip()]
+    assert len(lines) == len(sessions)
+    for i, (line, s) in enumerate(zip(lines, sessions)):
+        got = canon_events(ref_js._decanon(json.loads(line))["events"])
+        assert got == s["events"], (s["corpus"], i)
+
+
+def test_js_flatten_matches_python_request_batch(zk):
+    """flatten.js (packets -> encode descriptors) must lay packets out exactly as encode.py does."""
+    from test_oracle_golden import unjson
+    g = json.load(open(os.path.join(GOLD, "ref_encode.json")))
+    src = open(os.path.join(ROOT, "node-zkstream_b200", "js", "flatten.js")).read()
+    for p in g["packets"]:
+        pkt = unjson(p["pkt"])
+        batch = zk.RequestBatch.from_packets([pkt], p["handshaking"], p["isServer"])
+        driver = src + r"""
+var fl = makeFlatten({ consts: requireShim('./zk-consts'), assert: requireShim('assert-plus'), Buffer: Buffer });
+var c = fl([%s], %s, %s);
+var ar = '';
+for (var i = 0; i < c.arena.length; ++i) ar += c.arena[i].toString('hex');
+var o = [];
+for (var k in c) if (k !== 'arena') o.push(jstr(k) + ':' + (typeof (c[k]) === 'number' ? c[k] : '[' + c[k].join(',') + ']'));
+print('{' + o.join(',') + ',"arena":"' + ar + '"}');
+""" % (ref_js.js_literal(pkt), "true" if p["handshaking"] else "false", "true" if p["isServer"] else "false")
+        got = json.loads(ref_js.run_js(driver))
+        assert got["arena"] == batch.arena.tobytes().hex(), pkt
+        for name, dt in zk._abi.REQ_COLS + zk._abi.ELEM_COLS + zk._abi.REQ_ACL_COLS:
+            want = np.ascontiguousarray(batch.cols[name], dtype=dt)
+            if name in ("zxid", "zxid2"):
+                want = want.view(np.int32)
+            assert [int(x) for x in want] == got[name], (name, pkt)
