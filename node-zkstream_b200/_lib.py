@@ -12,7 +12,8 @@ from . import _abi
 from .columns import Columns
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libzkbatch.so")
+# ZKBATCH_LIB points at an alternative build of the same library (e.g. a profiling build)
+LIB_PATH = os.environ.get("ZKBATCH_LIB") or os.path.join(_HERE, "libzkbatch.so")
 _lib = None
 
 

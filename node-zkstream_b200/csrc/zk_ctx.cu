@@ -89,6 +89,13 @@ ZKB_EXPORT const char *zkb_last_error(const zkb_ctx *ctx) { return ctx ? ctx->er
 ZKB_EXPORT uint64_t zkb_kernel_launches(const zkb_ctx *ctx) { return ctx ? ctx->launches : 0; }
 ZKB_EXPORT uint64_t zkb_split_fixups(const zkb_ctx *ctx) { return ctx ? ctx->split_fixups : 0; }
 ZKB_EXPORT uint64_t zkb_last_slow_frames(const zkb_ctx *ctx) { return ctx ? ctx->slow_frames : 0; }
+#ifdef ZK_PROFILE_PHASES
+/* profiling builds only (not part of include/zkbatch.h) */
+extern "C" __attribute__((visibility("default"))) void zkb_debug_phase_cycles(const zkb_ctx *ctx, unsigned long long out[8])
+{
+	memcpy(out, ctx->prof, sizeof (ctx->prof));
+}
+#endif
 ZKB_EXPORT int zkb_ctx_set_timing(zkb_ctx *ctx, int on)
 {
 	if (!ctx) return ZKB_EINVAL;

@@ -58,12 +58,34 @@ __device__ __forceinline__ bool op_known(int32_t v)
 	return (v >= 0 && v <= 14 && v != 10) || (v >= 100 && v <= 102) || v == -10 || v == -11 || v == -1;
 }
 
-__device__ __forceinline__ uint4 ld_stream16(const uint4 *p)
+
+/* ---- TMA bulk copy global -> shared, completion on an mbarrier ------------------------- */
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
 {
-	uint4 r;
-	asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-	    : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-	return r;
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+	    :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+	asm volatile(
+	    "{\n"
+	    ".reg .pred p;\n"
+	    "ZK_WAIT_%=:\n"
+	    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	    "@p bra ZK_DONE_%=;\n"
+	    "bra ZK_WAIT_%=;\n"
+	    "ZK_DONE_%=:\n"
+	    "}\n" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 
 /* look-back descriptors: one 128-bit relaxed gpu-scope access each way (never cached in
@@ -1191,8 +1213,15 @@ __device__ int fast_request(ChunkSm &c, uint32_t pr, uint32_t size, FrameCols &o
 		if (!f.strvec<M>(o.a1)) return false;
 		if (!f.strvec<M>(o.err)) return false;
 		break;
-	default:
-		return -1;   /* PING, CLOSE_SESSION and unknown types throw in the reference */
+	default: {
+		/* readRequest throws 'Unsupported opcode' for everything else (zk-buffer.js:91-92),
+		 * PING and CLOSE_SESSION included: same answer the generic parser gives */
+		const int known = op_known(op) ? op : ZKB_OP_NONE;
+		o.xid = xid;
+		o.meta = ZKB_ST_BAD_DECODE | ((uint32_t)(uint8_t)(int8_t)known << 8) | ((uint32_t)ZKB_KIND_REQUEST << 16) |
+		    (DETAIL(ZKB_CAUSE_UNSUPPORTED, ZKB_F_OPCODE) << 24);
+		return 1;
+	}
 	}
 	o.xid = xid;
 	o.meta = ZKB_ST_OK | ((uint32_t)(uint8_t)(int8_t)op << 8) | ((uint32_t)ZKB_KIND_REQUEST << 16);
@@ -1240,37 +1269,44 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane)
 
 #define ZK_SPIN_LIMIT (1u << 26)
 
-/* One warp per 8 KiB chunk; warps never wait for each other except through the look-back. */
-__global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
-{
-	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
-	const uint32_t lane = threadIdx.x & 31;
-	ChunkSm &c = sm_all[threadIdx.x >> 5];
+/* Build with -DZK_PROFILE_PHASES to accumulate, per chunk, the SM cycles a decode warp spends
+ * in each phase (ticket, staging wait, frame loop, counts, look-back, emission) into
+ * zk_ctrl::prof; read them with zkb_debug_phase_cycles().  Off in normal builds. */
+#ifdef ZK_PROFILE_PHASES
+#define ZK_T(i) const long long zk_t##i = clock64()
+#define ZK_ACC(slot, a, b) do { if (lane == 0) atomicAdd(&a_ctrl_prof[slot], (unsigned long long)((b) - (a))); } while (0)
+#else
+#define ZK_T(i) do { } while (0)
+#define ZK_ACC(slot, a, b) do { } while (0)
+#endif
 
-	uint32_t chunk = 0;
-	if (lane == 0) chunk = atomicAdd(&a.ctrl->ticket, 1u);
-	chunk = __shfl_sync(0xffffffffu, chunk, 0);
-	if (chunk >= a.n_chunks) return;
+/* Everything one warp does for one 8 KiB chunk.  `phase` is the parity of the warp's
+ * mbarrier for this use (it flips every chunk). */
+__device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
+    const uint32_t chunk, const uint32_t lane, const long long zk_t0)
+{
+#ifdef ZK_PROFILE_PHASES
+	unsigned long long *a_ctrl_prof = a.ctrl->prof;
+#endif
+	(void)zk_t0;
+	ZK_T(1);
 	const uint64_t cs = (uint64_t)chunk << ZK_CHUNK_LOG2;
 	const uint64_t avail = a.nbytes_pad - cs;
 	const uint32_t wlen = avail < (uint64_t)ZK_WIN ? (uint32_t)avail : ZK_WIN;
 
-	/* ---- stage the chunk: 16-byte coalesced streaming loads, 6 in flight per lane ---- */
-	{
-		const uint4 *src = reinterpret_cast<const uint4 *>(a.bytes + cs);
-		uint4 *dst = reinterpret_cast<uint4 *>(c.tile);
-		const uint32_t nvec = wlen >> 4;
-		uint32_t i = lane;
-		for (; i + 5 * 32 < nvec; i += 6 * 32) {
-			uint4 v0 = ld_stream16(src + i), v1 = ld_stream16(src + i + 32), v2 = ld_stream16(src + i + 64);
-			uint4 v3 = ld_stream16(src + i + 96), v4 = ld_stream16(src + i + 128), v5 = ld_stream16(src + i + 160);
-			dst[i] = v0; dst[i + 32] = v1; dst[i + 64] = v2; dst[i + 96] = v3; dst[i + 128] = v4; dst[i + 160] = v5;
-		}
-		for (; i < nvec; i += 32) dst[i] = ld_stream16(src + i);
-		if (lane == 0) *reinterpret_cast<uint4 *>(c.tile + (nvec << 4)) = make_uint4(0, 0, 0, 0);
-		for (uint32_t w = lane; w < ZK_BMW; w += 32) {
-			c.m_buf[w] = 0; c.m_acl[w] = 0; c.m_stat[w] = 0; c.sub0[w] = 0; c.sub1[w] = 0; c.fstart[w] = 0;
-		}
+	/* ---- stage the chunk: one TMA bulk copy (global -> shared, completion on an mbarrier)
+	 * issued by lane 0; while it is in flight the warp clears its bitmaps and fetches the
+	 * chunk's frame range and first frame rows, so those round trips overlap the copy ---- */
+	if (lane == 0) {
+		/* the previous chunk's reads of this tile (generic proxy) are done: order them before
+		 * the async-proxy write that refills it */
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+		mbar_expect_tx(bar, wlen);
+		bulk_g2s(c.tile, a.bytes + cs, wlen, bar);
+		*reinterpret_cast<uint4 *>(c.tile + wlen) = make_uint4(0, 0, 0, 0);
+	}
+	for (uint32_t w = lane; w < ZK_BMW; w += 32) {
+		c.m_buf[w] = 0; c.m_acl[w] = 0; c.m_stat[w] = 0; c.sub0[w] = 0; c.sub1[w] = 0; c.fstart[w] = 0;
 	}
 	Rd rd;
 	rd.sm = c.tile; rd.lo = cs; rd.wlen = wlen; rd.g = a.bytes;
@@ -1280,7 +1316,17 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 	const uint32_t f0 = a.g_base[g0];
 	const uint32_t f1 = (g1 < a.n_gran) ? a.g_base[g1] : (uint32_t)a.n_frames;
 	const uint32_t nfr = f1 - f0;
+	/* first round's rows, fetched before the tile has landed */
+	uint64_t pf_off = 0; int32_t pf_len = 0; uint32_t pf_s = 0;
+	if (lane < nfr) {
+		pf_off = a.o.frame_off[f0 + lane];
+		pf_len = a.o.frame_len[f0 + lane];
+		pf_s = a.o.session[f0 + lane];
+	}
 	__syncwarp();
+	ZK_T(2);
+	mbar_wait(bar, phase);
+	ZK_T(3);
 
 	/* ---- frames: lane k handles frames f0+k, f0+k+32, ... ---- */
 	Parsed lp;                       /* the chunk's long frame (reaches past the tile), if this lane has it */
@@ -1291,9 +1337,9 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 		const uint32_t k = k0 + lane;
 		if (k >= nfr) continue;
 		const uint32_t f = f0 + k;
-		const uint64_t foff = a.o.frame_off[f];
-		const int32_t flen = a.o.frame_len[f];
-		const uint32_t s = a.o.session[f];
+		const uint64_t foff = k0 ? a.o.frame_off[f] : pf_off;
+		const int32_t flen = k0 ? a.o.frame_len[f] : pf_len;
+		const uint32_t s = k0 ? a.o.session[f] : pf_s;
 		const uint32_t rel = (uint32_t)(foff - cs);
 		atomicOr(&c.fstart[rel >> 7], 1u << ((rel >> 2) & 31));
 		const bool inwin = rel + 4u + (uint32_t)flen <= wlen;
@@ -1332,6 +1378,7 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 		a.o.a1[f] = o.a1;
 	}
 	__syncwarp();
+	ZK_T(4);
 	n_slow = warp_sum(n_slow);
 	if (lane == 0 && n_slow) atomicAdd(&a.ctrl->n_slow, (unsigned long long)n_slow);
 
@@ -1359,32 +1406,49 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 	 * A chunk's descriptor is one aligned 16-byte word { state, stat, buf, acl } written and
 	 * read with single 128-bit accesses, so state and counts always belong together: first
 	 * the chunk's own totals (AGG), later its inclusive prefix (PFX). ---- */
+	ZK_T(5);
 	uint32_t e0 = 0, e1 = 0, e2 = 0;
 	if (chunk > 0) {
 		if (lane == 0) st_desc(a.lb + chunk, make_uint4(ZK_LB_AGG, ts, tb, ta));
+		/* Each round looks at the 128 chunks before position j: lane l reads chunks j-l,
+		 * j-32-l, j-64-l, j-96-l with four independent loads (one round trip).  It can finish
+		 * as soon as the nearest full prefix has no unpublished chunk in front of it. */
 		int64_t j = (int64_t)chunk - 1;
-		uint32_t spins = 0, ns_sleep = 16;
+		uint32_t spins = 0, ns_sleep = 128;
 		for (;;) {
-			const int64_t idx = j - (int64_t)lane;
-			uint4 d = make_uint4(ZK_LB_PFX, 0, 0, 0);
-			if (idx >= 0) d = ld_desc(a.lb + idx);
-			if (__any_sync(0xffffffffu, d.x == ZK_LB_EMPTY)) {
+			uint4 d[4];
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+				const int64_t idx = j - 32 * q - (int64_t)lane;
+				d[q] = make_uint4(ZK_LB_PFX, 0, 0, 0);
+				if (idx >= 0) d[q] = ld_desc(a.lb + idx);
+			}
+			bool done = false, wait = false;
+			uint32_t s0 = 0, s1 = 0, s2 = 0;
+#pragma unroll
+			for (int q = 0; q < 4; ++q) {
+				if (done || wait) continue;
+				const uint32_t pm = __ballot_sync(0xffffffffu, d[q].x == ZK_LB_PFX);
+				const uint32_t em = __ballot_sync(0xffffffffu, d[q].x == ZK_LB_EMPTY);
+				const int first = __ffs(pm) - 1;       /* nearest full prefix in this group */
+				const int hole = __ffs(em) - 1;        /* nearest chunk that has published nothing */
+				if (hole >= 0 && (first < 0 || hole < first)) { wait = true; continue; }
+				const bool use = (first < 0 || (int)lane <= first);
+				s0 += use ? d[q].y : 0u; s1 += use ? d[q].z : 0u; s2 += use ? d[q].w : 0u;
+				if (first >= 0) done = true;
+			}
+			if (wait) {
 				if (++spins > ZK_SPIN_LIMIT) {
 					if (lane == 0) atomicOr(&a.ctrl->error, ZK_DERR_LOOKBACK);
 					break;
 				}
 				__nanosleep(ns_sleep);
-				if (ns_sleep < 512) ns_sleep <<= 1;
+				if (ns_sleep < 1024) ns_sleep <<= 1;
 				continue;
 			}
-			const uint32_t pm = __ballot_sync(0xffffffffu, d.x == ZK_LB_PFX);
-			const int first = __ffs(pm) - 1;   /* nearest predecessor holding a full prefix */
-			const bool use = (first < 0 || (int)lane <= first);
-			e0 += warp_sum(use ? d.y : 0u);
-			e1 += warp_sum(use ? d.z : 0u);
-			e2 += warp_sum(use ? d.w : 0u);
-			if (first >= 0) break;
-			j -= 32;
+			e0 += warp_sum(s0); e1 += warp_sum(s1); e2 += warp_sum(s2);
+			if (done) break;
+			j -= 128;
 		}
 	}
 	if (lane == 0) {
@@ -1395,6 +1459,9 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 			a.ctrl->n_acl = (unsigned long long)e2 + ta;
 		}
 	}
+	ZK_T(6);
+	ZK_ACC(0, zk_t0, zk_t1); ZK_ACC(1, zk_t1, zk_t2); ZK_ACC(2, zk_t2, zk_t3); ZK_ACC(3, zk_t3, zk_t4);
+	ZK_ACC(4, zk_t4, zk_t5); ZK_ACC(5, zk_t5, zk_t6);
 	if (ts + tb + ta == 0) return;
 
 	/* ---- emit: compact each bitmap, lane w owns bitmap word w (128 input bytes) ---- */
@@ -1485,6 +1552,38 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 	/* the long frame's rows come last: it is the chunk's last frame */
 	if (lp.n_stat | lp.n_buf | lp.n_acl)
 		emit_side(rd, a, l_foff, l_flen, lp, l_f, e0 + ns, e1 + nb, e2 + na);
+	ZK_T(7);
+	ZK_ACC(6, zk_t6, zk_t7);
+#ifdef ZK_PROFILE_PHASES
+	if (lane == 0) atomicAdd(&a_ctrl_prof[7], 1ull);
+#endif
+}
+
+/* One CTA = ZK_DEC_WARPS warps = that many consecutive chunks.  Chunks are handed out in
+ * launch order through one ticket per CTA, so every chunk a warp may wait for in the
+ * look-back belongs to a CTA that is already running: no deadlock whatever order the
+ * hardware starts CTAs in.  (Measured alternatives: a ticket per warp, and persistent warps
+ * that loop over tickets, were both slower — see profiles/r1_notes.md.)  After the ticket
+ * the warps never wait for each other except through the look-back. */
+__global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
+{
+	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
+	__shared__ __align__(8) uint64_t s_bar[ZK_DEC_WARPS];
+	__shared__ uint32_t s_ticket;
+	const uint32_t lane = threadIdx.x & 31;
+	ChunkSm &c = sm_all[threadIdx.x >> 5];
+	uint64_t *bar = &s_bar[threadIdx.x >> 5];
+#ifdef ZK_PROFILE_PHASES
+	const long long t0 = clock64();
+#else
+	const long long t0 = 0;
+#endif
+	if (lane == 0) mbar_init(bar, 1);
+	if (threadIdx.x == 0) s_ticket = atomicAdd(&a.ctrl->ticket, 1u);
+	__syncthreads();
+	const uint32_t chunk = s_ticket * ZK_DEC_WARPS + (threadIdx.x >> 5);
+	if (chunk >= a.n_chunks) return;
+	decode_chunk(a, c, bar, 0, chunk, lane, t0);
 }
 
 /* ================================================================================== */
@@ -1697,7 +1796,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, out);
 	const uint32_t split_blocks = (L.n_gran + 127) / 128;
 	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->ticket, 0, sizeof (unsigned int), ctx->stream));
-	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long), ctx->stream));
+	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long) * 9, ctx->stream));
 	ZK_EV(ctx, 2);
 	k_split<MODE_EMIT><<<split_blocks, 128, 0, ctx->stream>>>(sa);
 	LAUNCH_CHECK(ctx);
@@ -1732,6 +1831,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		return ZKB_EINTERNAL;
 	}
 	ctx->slow_frames = ctx->h_ctrl->n_slow;
+	memcpy(ctx->prof, ctx->h_ctrl->prof, sizeof (ctx->prof));
 	out->n_stat = ctx->h_ctrl->n_stat;
 	out->n_buf = ctx->h_ctrl->n_buf;
 	out->n_acl = ctx->h_ctrl->n_acl;

@@ -39,6 +39,7 @@ struct zk_ctrl {
 	unsigned long long n_stat, n_buf, n_acl;
 	unsigned long long enc_bytes;
 	unsigned long long n_slow;   /* frames that needed the generic (exact) parser */
+	unsigned long long prof[8];  /* ZK_PROFILE_PHASES builds: cycles per decode phase, chunk count */
 };
 
 struct zkb_ctx {
@@ -48,6 +49,7 @@ struct zkb_ctx {
 	uint64_t      launches;
 	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
 	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
+	unsigned long long prof[8];
 	/* device scratch (grown on demand, never shrunk) */
 	void         *d_scratch;   size_t d_scratch_bytes;
 	zk_ctrl      *d_ctrl;

@@ -1,0 +1,39 @@
+"""Development aid: per-phase SM cycles of k_decode, from a library built with
+-DZK_PROFILE_PHASES (see the comment in csrc/zk_decode.cu).
+
+    ZKBATCH_LIB=tools/libzkbatch_prof.so python tools/phase_profile.py [gb]
+"""
+import ctypes as C
+import importlib
+import sys
+
+import numpy as np
+
+sys.path.insert(0, ".")
+zk = importlib.import_module("node-zkstream_b200")
+synth = importlib.import_module("node-zkstream_b200.synth")
+dev = importlib.import_module("node-zkstream_b200.device")
+
+gb = float(sys.argv[1]) if len(sys.argv) > 1 else 1.0
+S = max(16, int(gb * 1e9 / 7.79e6))
+pc = synth.native_cfg2(1, S, 20000)
+ctx = zk.Context(0)
+lib = ctx._lib
+lib.zkb_debug_phase_cycles.argtypes = [C.c_void_p, C.POINTER(C.c_ulonglong * 8)]
+device = "cuda:0"
+names = ["ticket", "issue+prefetch", "tile wait", "frame loop", "counts", "look-back", "emission", "chunks"]
+for label, data, off, fl, xt in (("request streams", pc.req, pc.req_off, pc.req_flags, None),
+                                 ("response streams", pc.rsp, pc.rsp_off, pc.rsp_flags, pc.xidtable())):
+    d = dev.to_device(data, device, pad=64)
+    ds = dev.DeviceSessions(data.size, off, fl, None, device)
+    dx = dev.DeviceXidTable(xt, device) if xt is not None else None
+    dc = dev.decode_dev_autosize(ctx, d, int(data.size), ds, dx, device=device)
+    for _ in range(3):
+        dev.decode_dev(ctx, d, int(data.size), ds, dx, dc)
+    out = (C.c_ulonglong * 8)()
+    lib.zkb_debug_phase_cycles(ctx._h, C.byref(out))
+    n = max(1, out[7])
+    tot = sum(out[i] for i in range(7))
+    print(label, "chunks", out[7], "avg cycles per chunk %.0f" % (tot / n))
+    for i in range(7):
+        print("   %-16s %8.0f cycles  %5.1f%%" % (names[i], out[i] / n, 100.0 * out[i] / max(tot, 1)))
