@@ -14,7 +14,8 @@ is one full pass of the hot path over that batch:
 
 `value` is whole-job decoded frames/s with the batch already resident in HBM (CUDA events
 on the codec's stream, max over ranks).  `e2e` is the same pass through the host-buffer
-entry points of the C ABI: pinned host bytes in, host columns out, all copies timed.
+entry point of the C ABI (zkb_replay_host: pinned host bytes in, host columns out, slices
+pipelined over upload / decode / download streams), all copies timed.
 `roofline` describes the dominant kernel (k_decode).  `cpu_baseline` and
 `--impl reference` time the CPU port of the reference's decode loop (oracle/zkoracle.c,
 faithful mode: 64 KiB chunks, per-frame copy + memmove as lib/zk-streams.js:55-59) on the
@@ -357,14 +358,19 @@ def run_ours(args, rank, local_rank, world):
 
     def step_e2e():
         nonlocal h2d, d2h
-        cr = ctx.decode_host(pc.req, pc.req_off, pc.req_flags, None, None, copy=False)
-        nfr = cr.n_frames
-        d2h_1 = cr.nbytes_columns()
-        xt = ctx.xidtab_build_host(cr, layout)
-        cs = ctx.decode_host(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt, copy=False)
-        h2d = nreq + nrsp + 2 * (S + 1) * 8 + 2 * S + 16 * nfr + 16 * S + 16 * S + xt.nops
-        d2h = d2h_1 + cs.nbytes_columns() + xt.nops
-        return nfr + cs.n_frames
+        tot = {"frames": 0, "d2h": 0, "ok": 0}
+
+        def on_slice(first, ns, rq, rs):
+            # the "result read": every slice's columns are on the host; touch the status column
+            tot["frames"] += rq.n_frames + rs.n_frames
+            tot["d2h"] += rq.nbytes_columns() + rs.nbytes_columns()
+            tot["ok"] += int((rs.meta & 0xff == 0).sum())
+
+        ctx.replay_host(pc.req, pc.req_off, pc.rsp, pc.rsp_off, layout.base, layout.count, on_slice,
+                        req_flags=pc.req_flags, rsp_flags=pc.rsp_flags, copy=False)
+        h2d = nreq + nrsp + 2 * (S + 1) * 8 + 2 * S + 16 * S
+        d2h = tot["d2h"]
+        return tot["frames"]
 
     step_e2e()
     barrier()

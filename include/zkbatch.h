@@ -318,6 +318,35 @@ int zkb_decode_dev(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbytes,
 int zkb_decode_host(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbytes,
     const zkb_sessions *sess, const zkb_xidtab *xid, zkb_decoded *out);
 
+/* ---- paired replay, pipelined over PCIe ------------------------------------------------ */
+
+/*
+ * What a capture replay does with one ZKEncodeStream/ZKDecodeStream pair per connection
+ * (lib/zk-streams.js:145 feeding lib/zk-buffer.js:288-290), for a whole capture in host
+ * memory: decode the client->server streams, derive each connection's xid -> opcode map from
+ * them, decode the server->client streams with that map.  Session i of `req` pairs with
+ * session i of `rsp`; xids [xid_base[i], xid_base[i] + xid_count[i]) are tracked per session.
+ *
+ * The sessions are cut into slices of about `slice_bytes` (0 = default, 256 MiB) and the
+ * slices flow through three CUDA streams — upload, decode, download — so the PCIe transfers of
+ * neighbouring slices overlap the kernels.  Results are handed to `cb` one slice at a time, in
+ * session order, as context-owned pinned host columns that stay valid until `cb` returns:
+ *   - `session` columns and all byte offsets (frame_off, buf_off, sess_consumed,
+ *     sess_bad_length_at) are global: they index the caller's session arrays and byte buffers;
+ *   - row references (stat_frame, buf_frame, acl_frame, sess_first_frame) are local to the
+ *     slice's own tables; sess_* arrays hold the slice's `nsessions` sessions.
+ * A non-zero return from `cb` stops the replay and is returned.  Pin the input buffers
+ * (cudaHostRegister / cudaHostAlloc) for full PCIe speed; pageable memory works, slower.
+ */
+typedef int (*zkb_slice_cb)(void *user, uint32_t first_session, uint32_t nsessions,
+    const zkb_decoded *req, const zkb_decoded *rsp);
+
+int zkb_replay_host(zkb_ctx *ctx,
+    const uint8_t *req_bytes, uint64_t req_nbytes, const zkb_sessions *req_sess,
+    const uint8_t *rsp_bytes, uint64_t rsp_nbytes, const zkb_sessions *rsp_sess,
+    const int32_t *xid_base, const uint32_t *xid_count, uint64_t slice_bytes,
+    zkb_slice_cb cb, void *user);
+
 /* ---- xid table ------------------------------------------------------------------------ */
 
 /*

@@ -65,6 +65,8 @@ class Requests(C.Structure):
                 ("acl_id_off", P), ("acl_id_len", P)]
 
 
+SLICE_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(Decoded), C.POINTER(Decoded))
+
 # every symbol include/zkbatch.h declares: (name, restype, argtypes)
 SYMBOLS = [
     ("zkb_ctx_create", C.c_int, [C.c_int, C.POINTER(P)]),
@@ -80,6 +82,8 @@ SYMBOLS = [
     ("zkb_decode_scratch_bytes", C.c_uint64, [C.c_uint64, C.c_uint32]),
     ("zkb_decode_dev", C.c_int, [P, P, C.c_uint64, C.POINTER(Sessions), C.POINTER(XidTab), C.POINTER(Decoded)]),
     ("zkb_decode_host", C.c_int, [P, P, C.c_uint64, C.POINTER(Sessions), C.POINTER(XidTab), C.POINTER(Decoded)]),
+    ("zkb_replay_host", C.c_int, [P, P, C.c_uint64, C.POINTER(Sessions), P, C.c_uint64, C.POINTER(Sessions),
+                                  P, P, C.c_uint64, SLICE_CB, P]),
     ("zkb_xidtab_build_host", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P]),
     ("zkb_xidtab_build_dev", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P]),
     ("zkb_xidtab_build_noalloc", C.c_int, [C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P, P,

@@ -176,6 +176,39 @@ class Context:
         del keep
         return Columns.from_struct(out, s.nsessions, copy=copy)
 
+    def replay_host(self, req, req_off, rsp, rsp_off, xid_base, xid_count, on_slice, req_flags=None,
+                    rsp_flags=None, req_hs=None, rsp_hs=None, slice_bytes=0, copy=True):
+        """Pipelined paired replay (zkb_replay_host).  on_slice(first_session, nsessions, req_cols,
+        rsp_cols) is called once per slice, in order; with copy=False the Columns are views that
+        die when on_slice returns.  Request streams default to ZKB_SESS_SERVER."""
+        req = np.ascontiguousarray(req, dtype=np.uint8)
+        rsp = np.ascontiguousarray(rsp, dtype=np.uint8)
+        n = len(req_off) - 1
+        if req_flags is None:
+            req_flags = np.full(n, _abi.SESS_SERVER, dtype=np.uint8)
+        s1, k1 = self._sessions(req.size, req_off, req_flags, req_hs)
+        s2, k2 = self._sessions(rsp.size, rsp_off, rsp_flags, rsp_hs)
+        xb = np.ascontiguousarray(xid_base, dtype=np.int32)
+        xc = np.ascontiguousarray(xid_count, dtype=np.uint32)
+        err = []
+
+        def _cb(user, first, ns, rq, rs):
+            try:
+                on_slice(int(first), int(ns), Columns.from_struct(rq.contents, int(ns), copy=copy),
+                         Columns.from_struct(rs.contents, int(ns), copy=copy))
+                return 0
+            except Exception as e:      # never let an exception cross the C frame
+                err.append(e)
+                return -1
+
+        cb = _abi.SLICE_CB(_cb)
+        rc = self._lib.zkb_replay_host(self._h, _ptr(req), req.size, C.byref(s1), _ptr(rsp), rsp.size,
+                                       C.byref(s2), xb.ctypes.data, xc.ctypes.data, int(slice_bytes), cb, None)
+        del k1, k2
+        if err:
+            raise err[0]
+        self._check(rc)
+
     def decode_dev(self, d_bytes, nbytes, d_sess, d_xid, d_out):
         """Raw device-pointer call (structs from _abi, filled by the caller)."""
         rc = self._lib.zkb_decode_dev(self._h, d_bytes, nbytes, C.byref(d_sess),

@@ -82,6 +82,17 @@ ZKB_EXPORT void zkb_ctx_destroy(zkb_ctx *ctx)
 	if (ctx->h_out) cudaFreeHost(ctx->h_out);
 	if (ctx->h_in) cudaFreeHost(ctx->h_in);
 	for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+	for (int i = 0; i < 2; i++) {
+		if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+		if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+		if (ctx->ev_out[i]) cudaEventDestroy(ctx->ev_out[i]);
+		if (ctx->rp_in[i]) cudaFree(ctx->rp_in[i]);
+		if (ctx->rp_out[i]) cudaFree(ctx->rp_out[i]);
+		if (ctx->rp_host[i]) cudaFreeHost(ctx->rp_host[i]);
+		if (ctx->rp_stage[i]) cudaFreeHost(ctx->rp_stage[i]);
+	}
+	if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
+	if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
 	delete ctx;
 }
 
@@ -424,4 +435,294 @@ ZKB_EXPORT int zkb_encode_host(zkb_ctx *ctx, const zkb_requests *req, const uint
 	ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	*out = h_bytes; *frame_off = h_fo; *status = h_st; *out_len = total;
 	return ZKB_OK;
+}
+
+/* ---- pipelined paired replay -------------------------------------------------------------- */
+
+/* slice-local -> global: byte offsets get the slice's byte base, sessions the session base */
+__global__ void k_rebase(zkb_decoded d, uint64_t byte_base, uint32_t sess_base, uint32_t nsess)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < d.n_frames) { d.frame_off[i] += byte_base; d.session[i] += sess_base; }
+	if (i < d.n_buf) d.buf_off[i] += byte_base;
+	if (i < nsess) {
+		d.sess_consumed[i] += byte_base;
+		if (d.sess_bad_length_at[i] != ZKB_NO_OFFSET) d.sess_bad_length_at[i] += byte_base;
+	}
+}
+
+struct ReplaySlice {
+	uint32_t s0, s1;
+	uint64_t req_lo, req_hi, rsp_lo, rsp_hi;
+	uint64_t nops;
+};
+
+struct SliceDev {      /* device pointers of one slice's inputs */
+	uint8_t *req, *rsp;
+	uint64_t *req_off, *rsp_off, *x_off;
+	uint8_t *req_flags, *rsp_flags;
+	uint32_t *req_hs, *rsp_hs, *x_count;
+	int32_t *x_base;
+	int8_t *x_ops;
+};
+
+static size_t carve_slice_in(SliceDev *d, uint8_t *base, const ReplaySlice &sl)
+{
+	Carver c = { base, 0 };
+	const uint32_t n = sl.s1 - sl.s0;
+	d->req = c.take<uint8_t>(sl.req_hi - sl.req_lo + 64);
+	d->rsp = c.take<uint8_t>(sl.rsp_hi - sl.rsp_lo + 64);
+	d->req_off = c.take<uint64_t>((uint64_t)n + 1); d->rsp_off = c.take<uint64_t>((uint64_t)n + 1);
+	d->x_off = c.take<uint64_t>(n);
+	d->req_flags = c.take<uint8_t>(n); d->rsp_flags = c.take<uint8_t>(n);
+	d->req_hs = c.take<uint32_t>(n); d->rsp_hs = c.take<uint32_t>(n); d->x_count = c.take<uint32_t>(n);
+	d->x_base = c.take<int32_t>(n);
+	d->x_ops = c.take<int8_t>(sl.nops);
+	return c.off;
+}
+
+/* decode one direction of a slice into ctx->rp_out[...] region starting at *cursor */
+static int replay_decode_dir(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes, const zkb_sessions *ds,
+    const zkb_xidtab *dx, uint8_t *out_base, size_t out_cap, size_t *used, zkb_decoded *dv)
+{
+	int rc;
+	uint64_t n_frames = 0;
+	const uint32_t nsess = ds->nsessions;
+	if ((rc = zk_split_device(ctx, d_bytes, nbytes, ds, &n_frames))) return rc;
+	uint64_t cs = n_frames < nbytes / 88 + 1 ? n_frames : nbytes / 88 + 1;
+	uint64_t cb = n_frames * 2 + nbytes / 64 + 16;
+	if (cb > nbytes / 4 + 1) cb = nbytes / 4 + 1;
+	uint64_t ca = n_frames / 2 + 16;
+	if (ca > nbytes / 12 + 1) ca = nbytes / 12 + 1;
+	for (int attempt = 0;; ++attempt) {
+		memset(dv, 0, sizeof (*dv));
+		size_t need = carve_decoded(dv, NULL, n_frames, cs, cb, ca, nsess);
+		if (need > out_cap) { *used = need; return ZKB_EOVERFLOW; }
+		carve_decoded(dv, out_base, n_frames, cs, cb, ca, nsess);
+		rc = zk_fields_device(ctx, d_bytes, nbytes, ds, dx, n_frames, dv);
+		if (rc == ZKB_EOVERFLOW && attempt == 0) { cs = dv->n_stat; cb = dv->n_buf; ca = dv->n_acl; continue; }
+		if (rc) return rc;
+		*used = need;
+		return ZKB_OK;
+	}
+}
+
+ZKB_EXPORT int zkb_replay_host(zkb_ctx *ctx,
+    const uint8_t *req_bytes, uint64_t req_nbytes, const zkb_sessions *req_sess,
+    const uint8_t *rsp_bytes, uint64_t rsp_nbytes, const zkb_sessions *rsp_sess,
+    const int32_t *xid_base, const uint32_t *xid_count, uint64_t slice_bytes,
+    zkb_slice_cb cb, void *user)
+{
+	int rc;
+	if (!ctx) return ZKB_EINVAL;
+	if (!req_sess || !rsp_sess || !req_sess->off || !rsp_sess->off || !xid_base || !xid_count || !cb ||
+	    req_sess->nsessions != rsp_sess->nsessions) {
+		snprintf(ctx->err, sizeof (ctx->err), "zkb_replay_host: bad arguments");
+		return ZKB_EINVAL;
+	}
+	const uint32_t nsess = req_sess->nsessions;
+	if (req_sess->off[0] != 0 || rsp_sess->off[0] != 0 || req_sess->off[nsess] != req_nbytes ||
+	    rsp_sess->off[nsess] != rsp_nbytes) {
+		snprintf(ctx->err, sizeof (ctx->err), "zkb_replay_host: session offsets do not cover the buffers");
+		return ZKB_EINVAL;
+	}
+	for (uint32_t s = 0; s < nsess; s++) {
+		if (req_sess->off[s] > req_sess->off[s + 1] || rsp_sess->off[s] > rsp_sess->off[s + 1]) {
+			snprintf(ctx->err, sizeof (ctx->err), "zkb_replay_host: session offsets not monotone");
+			return ZKB_EINVAL;
+		}
+	}
+	ZK_CUDA(ctx, cudaSetDevice(ctx->device));
+	if (!ctx->s_in) {
+		ZK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
+		ZK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+		for (int i = 0; i < 2; i++) {
+			ZK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+			ZK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+			ZK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_out[i], cudaEventDisableTiming));
+		}
+	}
+	if (slice_bytes == 0) slice_bytes = 256ull << 20;
+
+	/* ---- cut the sessions into slices ---- */
+	uint32_t nslices = 0, cap_slices = 16;
+	ReplaySlice *sl = (ReplaySlice *)malloc(cap_slices * sizeof (ReplaySlice));
+	if (!sl) return ZKB_ENOMEM;
+	size_t max_in = 0;
+	uint32_t max_n = 0;
+	for (uint32_t s = 0; s < nsess || nslices == 0;) {
+		ReplaySlice x;
+		x.s0 = s;
+		uint64_t bytes = 0;
+		x.nops = 0;
+		while (s < nsess) {
+			uint64_t b = (req_sess->off[s + 1] - req_sess->off[s]) + (rsp_sess->off[s + 1] - rsp_sess->off[s]);
+			if (s > x.s0 && bytes + b > slice_bytes) break;
+			bytes += b; x.nops += xid_count[s]; s++;
+		}
+		x.s1 = s;
+		x.req_lo = req_sess->off[x.s0]; x.req_hi = req_sess->off[x.s1];
+		x.rsp_lo = rsp_sess->off[x.s0]; x.rsp_hi = rsp_sess->off[x.s1];
+		if (nslices == cap_slices) {
+			cap_slices *= 2;
+			ReplaySlice *n2 = (ReplaySlice *)realloc(sl, cap_slices * sizeof (ReplaySlice));
+			if (!n2) { free(sl); return ZKB_ENOMEM; }
+			sl = n2;
+		}
+		sl[nslices++] = x;
+		SliceDev tmp;
+		size_t need = carve_slice_in(&tmp, NULL, x);
+		if (need > max_in) max_in = need;
+		if (x.s1 - x.s0 > max_n) max_n = x.s1 - x.s0;
+		if (nsess == 0) break;
+	}
+
+#define RP_FAIL(code) do { rc = (code); goto out; } while (0)
+#define RP_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { \
+	snprintf(ctx->err, sizeof (ctx->err), "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+	RP_FAIL(ZKB_ECUDA); } } while (0)
+
+	rc = ZKB_OK;
+	{
+		/* buffers: two slice inputs, two slice outputs (device + pinned mirror), staging */
+		const size_t stage_need = zk_align_up(((size_t)max_n + 1) * 8, 256) * 3 + 4096;
+		size_t out_guess = (size_t)(slice_bytes + slice_bytes / 4) + (64u << 20);
+		for (int i = 0; i < 2; i++) {
+			if ((rc = zk_ensure(ctx, &ctx->rp_in[i], &ctx->rp_in_bytes[i], max_in + 4096, 0))) goto out;
+			if ((rc = zk_ensure(ctx, &ctx->rp_stage[i], &ctx->rp_stage_bytes[i], stage_need, 1))) goto out;
+			if (ctx->rp_out_bytes[i] < out_guess) {
+				if ((rc = zk_ensure(ctx, &ctx->rp_out[i], &ctx->rp_out_bytes[i], out_guess, 0))) goto out;
+				if ((rc = zk_ensure(ctx, &ctx->rp_host[i], &ctx->rp_host_bytes[i], out_guess, 1))) goto out;
+			}
+		}
+		SliceDev sd[2];
+		zkb_decoded hreq[2], hrsp[2];
+		uint32_t pending = UINT32_MAX;     /* slice whose download is in flight */
+
+		/* upload of slice i into buffer i & 1 (asynchronous, on s_in) */
+		auto upload = [&](uint32_t i) -> int {
+			const int b = i & 1;
+			const ReplaySlice &x = sl[i];
+			const uint32_t n = x.s1 - x.s0;
+			carve_slice_in(&sd[b], (uint8_t *)ctx->rp_in[b], x);
+			/* rebased session offsets and the table layout are staged in pinned memory */
+			uint8_t *st = (uint8_t *)ctx->rp_stage[b];
+			uint64_t *h_req_off = (uint64_t *)st;
+			uint64_t *h_rsp_off = (uint64_t *)(st + zk_align_up(((size_t)n + 1) * 8, 256));
+			uint64_t *h_x_off = (uint64_t *)(st + 2 * zk_align_up(((size_t)n + 1) * 8, 256));
+			uint64_t xo = 0;
+			for (uint32_t k = 0; k <= n; k++) {
+				h_req_off[k] = req_sess->off[x.s0 + k] - x.req_lo;
+				h_rsp_off[k] = rsp_sess->off[x.s0 + k] - x.rsp_lo;
+				if (k < n) { h_x_off[k] = xo; xo += xid_count[x.s0 + k]; }
+			}
+			cudaError_t e;
+#define UP(dst, src, bytes) if ((bytes) > 0 && (e = cudaMemcpyAsync(dst, src, (size_t)(bytes), cudaMemcpyHostToDevice, ctx->s_in)) != cudaSuccess) { \
+	snprintf(ctx->err, sizeof (ctx->err), "zkb_replay_host upload: %s", cudaGetErrorString(e)); return ZKB_ECUDA; }
+			UP(sd[b].req, req_bytes + x.req_lo, x.req_hi - x.req_lo);
+			UP(sd[b].rsp, rsp_bytes + x.rsp_lo, x.rsp_hi - x.rsp_lo);
+			UP(sd[b].req_off, h_req_off, ((size_t)n + 1) * 8);
+			UP(sd[b].rsp_off, h_rsp_off, ((size_t)n + 1) * 8);
+			UP(sd[b].x_off, h_x_off, (size_t)n * 8);
+			if (req_sess->flags) UP(sd[b].req_flags, req_sess->flags + x.s0, n);
+			if (rsp_sess->flags) UP(sd[b].rsp_flags, rsp_sess->flags + x.s0, n);
+			if (req_sess->handshake_frames) UP(sd[b].req_hs, req_sess->handshake_frames + x.s0, (size_t)n * 4);
+			if (rsp_sess->handshake_frames) UP(sd[b].rsp_hs, rsp_sess->handshake_frames + x.s0, (size_t)n * 4);
+			UP(sd[b].x_base, xid_base + x.s0, (size_t)n * 4);
+			UP(sd[b].x_count, xid_count + x.s0, (size_t)n * 4);
+#undef UP
+			if ((e = cudaEventRecord(ctx->ev_in[b], ctx->s_in)) != cudaSuccess) return ZKB_ECUDA;
+			return ZKB_OK;
+		};
+		auto deliver = [&](uint32_t i) -> int {
+			const int b = i & 1;
+			cudaError_t e = cudaEventSynchronize(ctx->ev_out[b]);
+			if (e != cudaSuccess) { snprintf(ctx->err, sizeof (ctx->err), "zkb_replay_host download: %s", cudaGetErrorString(e)); return ZKB_ECUDA; }
+			return cb(user, sl[i].s0, sl[i].s1 - sl[i].s0, &hreq[b], &hrsp[b]);
+		};
+
+		if (nsess) {
+			/* the input buffer may still be read by nothing: first slice goes straight up */
+			if ((rc = upload(0))) goto out;
+		}
+		for (uint32_t i = 0; i < nslices && nsess; i++) {
+			const int b = i & 1;
+			const ReplaySlice &x = sl[i];
+			const uint32_t n = x.s1 - x.s0;
+			/* next slice's upload runs under this slice's kernels; its buffer was last read by
+			 * slice i-1's kernels, which have finished (the decode calls below are synchronous) */
+			if (i + 1 < nslices && (rc = upload(i + 1))) goto out;
+			RP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[b], 0));
+			/* this slice's device outputs were last downloaded for slice i-2 */
+			if (i >= 2) RP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_out[b], 0));
+
+			zkb_sessions ds_req = { n, sd[b].req_off, req_sess->flags ? sd[b].req_flags : NULL,
+			    req_sess->handshake_frames ? sd[b].req_hs : NULL };
+			zkb_sessions ds_rsp = { n, sd[b].rsp_off, rsp_sess->flags ? sd[b].rsp_flags : NULL,
+			    rsp_sess->handshake_frames ? sd[b].rsp_hs : NULL };
+			zkb_xidtab dx;
+			dx.base = sd[b].x_base; dx.count = sd[b].x_count; dx.off = sd[b].x_off; dx.ops = sd[b].x_ops; dx.nops = x.nops;
+			zkb_decoded dreq, drsp;
+			size_t used_req = 0, used_rsp = 0;
+			for (int attempt = 0;; ++attempt) {
+				rc = replay_decode_dir(ctx, sd[b].req, x.req_hi - x.req_lo, &ds_req, NULL,
+				    (uint8_t *)ctx->rp_out[b], ctx->rp_out_bytes[b], &used_req, &dreq);
+				if (rc == ZKB_OK) {
+					used_req = zk_align_up(used_req, 256);
+					if ((rc = zk_xidtab_build_device(ctx, &dreq, n, &dx, sd[b].x_ops))) goto out;
+					rc = replay_decode_dir(ctx, sd[b].rsp, x.rsp_hi - x.rsp_lo, &ds_rsp, x.nops ? &dx : NULL,
+					    (uint8_t *)ctx->rp_out[b] + used_req, ctx->rp_out_bytes[b] - used_req, &used_rsp, &drsp);
+				}
+				if (rc == ZKB_EOVERFLOW && attempt < 3) {
+					/* the slice needs more room than estimated: wait for the other buffer's
+					 * download, then grow this pair (device + pinned mirror) */
+					if (pending != UINT32_MAX) { int r2 = deliver(pending); pending = UINT32_MAX; if (r2) RP_FAIL(r2); }
+					RP_CUDA(cudaStreamSynchronize(ctx->s_out));
+					const size_t want = (used_req + used_rsp) * 2 + (64u << 20);
+					if ((rc = zk_ensure(ctx, &ctx->rp_out[b], &ctx->rp_out_bytes[b], want, 0))) goto out;
+					if ((rc = zk_ensure(ctx, &ctx->rp_host[b], &ctx->rp_host_bytes[b], want, 1))) goto out;
+					continue;
+				}
+				if (rc) goto out;
+				break;
+			}
+			const uint64_t m1 = dreq.n_frames > dreq.n_buf ? dreq.n_frames : dreq.n_buf;
+			const uint64_t m2 = drsp.n_frames > drsp.n_buf ? drsp.n_frames : drsp.n_buf;
+			k_rebase<<<(unsigned)(((m1 > n ? m1 : n) + 255) / 256), 256, 0, ctx->stream>>>(dreq, x.req_lo, x.s0, n);
+			k_rebase<<<(unsigned)(((m2 > n ? m2 : n) + 255) / 256), 256, 0, ctx->stream>>>(drsp, x.rsp_lo, x.s0, n);
+			ctx->launches += 2;
+			RP_CUDA(cudaGetLastError());
+			RP_CUDA(cudaEventRecord(ctx->ev_done[b], ctx->stream));
+
+			/* download on s_out: exact row counts, into this buffer's pinned mirror */
+			RP_CUDA(cudaStreamWaitEvent(ctx->s_out, ctx->ev_done[b], 0));
+			{
+				cudaStream_t keep = ctx->stream;
+				ctx->stream = ctx->s_out;      /* copy_decoded_d2h queues on ctx->stream */
+				memset(&hreq[b], 0, sizeof (zkb_decoded)); memset(&hrsp[b], 0, sizeof (zkb_decoded));
+				size_t h1 = carve_decoded(&hreq[b], (uint8_t *)ctx->rp_host[b], dreq.n_frames, dreq.n_stat, dreq.n_buf, dreq.n_acl, n);
+				carve_decoded(&hrsp[b], (uint8_t *)ctx->rp_host[b] + zk_align_up(h1, 256), drsp.n_frames, drsp.n_stat, drsp.n_buf, drsp.n_acl, n);
+				rc = copy_decoded_d2h(ctx, &dreq, &hreq[b], n);
+				if (!rc) rc = copy_decoded_d2h(ctx, &drsp, &hrsp[b], n);
+				ctx->stream = keep;
+				if (rc) goto out;
+			}
+			RP_CUDA(cudaEventRecord(ctx->ev_out[b], ctx->s_out));
+
+			/* hand over the previous slice while this one downloads */
+			if (pending != UINT32_MAX) { int r2 = deliver(pending); pending = UINT32_MAX; if (r2) RP_FAIL(r2); }
+			pending = i;
+			/* the kernels of this slice are done (decode calls are synchronous): its input buffer
+			 * is free for slice i+2, which upload() will queue in the next iteration */
+		}
+		if (pending != UINT32_MAX) { int r2 = deliver(pending); if (r2) RP_FAIL(r2); }
+	}
+out:
+	cudaStreamSynchronize(ctx->s_in);
+	cudaStreamSynchronize(ctx->s_out);
+	cudaStreamSynchronize(ctx->stream);
+	free(sl);
+	return rc;
+#undef RP_FAIL
+#undef RP_CUDA
 }

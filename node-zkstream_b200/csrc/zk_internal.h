@@ -60,6 +60,13 @@ struct zkb_ctx {
 	void         *h_out;       size_t h_out_bytes;     /* pinned mirror of d_out */
 	void         *h_in;        size_t h_in_bytes;      /* pinned bounce buffer for small arrays */
 	int           sm_count;
+	/* zkb_replay_host: upload / download streams, double-buffered slices */
+	cudaStream_t  s_in, s_out;
+	cudaEvent_t   ev_in[2], ev_done[2], ev_out[2];
+	void         *rp_in[2];    size_t rp_in_bytes[2];    /* device: slice inputs */
+	void         *rp_out[2];   size_t rp_out_bytes[2];   /* device: slice outputs */
+	void         *rp_host[2];  size_t rp_host_bytes[2];  /* pinned: slice results */
+	void         *rp_stage[2]; size_t rp_stage_bytes[2]; /* pinned: rebased session arrays */
 	/* optional per-phase CUDA-event timing (zkb_ctx_set_timing) */
 	int           timing;
 	cudaEvent_t   ev[6];          /* split begin/end, emit begin/end, decode begin/end */

@@ -278,3 +278,27 @@ def test_large_cfg1_properties(ctx, synth):
     assert np.array_equal(cols.buf_off[1:], cols.frame_off[1:] + 24)
     assert (cols.dataLength == 256).all() and np.array_equal(cols.stat_frame, np.arange(1, 1000001, dtype=np.uint32))
     assert int(cols.sess_consumed[0]) == data.size
+
+
+def test_replay_host_pipelined_matches_oracle(ctx, oracle, synth):
+    """zkb_replay_host: slices flow through upload/decode/download streams; put back together the
+    slices must equal one oracle decode of each direction (xid table derived from the requests)."""
+    shard = importlib.import_module("node-zkstream_b200.shard")
+    pc = synth.native_cfg2(99, 37, 900)
+    n = pc.nsessions
+    layout = zk.XidTable(np.zeros(n, np.int32), np.full(n, pc.frames, np.uint32))
+    want_req = oracle.decode(pc.req, pc.req_off, pc.req_flags, None, None)
+    want_rsp = oracle.decode(pc.rsp, pc.rsp_off, pc.rsp_flags, None, oracle.xidtab_build(want_req, layout))
+    for slice_bytes in (0, 1 << 20, 300000):          # one slice, a few, many (forces buffer reuse)
+        got = []
+        ctx.replay_host(pc.req, pc.req_off, pc.rsp, pc.rsp_off, layout.base, layout.count,
+                        lambda first, ns, rq, rs: got.append((first, ns, rq, rs)), slice_bytes=slice_bytes)
+        assert [g[0] for g in got] == sorted(g[0] for g in got) and sum(g[1] for g in got) == n
+        if slice_bytes:
+            assert len(got) > 1
+        zeros = [0] * len(got)
+        req = shard.merge([g[2] for g in got], zeros, zeros)
+        rsp = shard.merge([g[3] for g in got], zeros, zeros)
+        assert req.diff(want_req) == [], slice_bytes
+        assert rsp.diff(want_rsp) == [], slice_bytes
+    assert (want_rsp.status == 0).all()
