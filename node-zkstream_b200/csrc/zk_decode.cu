@@ -693,15 +693,19 @@ enum { VEC_NONE = 0, VEC_STR1 = 1, VEC_ACL = 2, VEC_STR3 = 3 };
  * Two fields never start in the same slot, and slot order is stream order, so compacting a
  * bitmap yields the chunk's rows already in (frame, read order) order.  sub0/sub1 keep the
  * low two bits of the byte position. */
+#ifndef ZK_CHUNK_LOG2
 #define ZK_CHUNK_LOG2  13
+#endif
 #define ZK_CHUNK       (1u << ZK_CHUNK_LOG2)
+#ifndef ZK_OVER
 #define ZK_OVER        768u
+#endif
 #define ZK_WIN         (ZK_CHUNK + ZK_OVER)
 #define ZK_SLOTS       (ZK_WIN / 4)
 #define ZK_BMW         (ZK_SLOTS / 32)
 #define ZK_DEC_WARPS   4
 
-struct ChunkSm {
+struct __align__(16) ChunkSm {
 	uint8_t  tile[ZK_WIN + 16];
 	uint32_t m_buf[ZK_BMW], m_acl[ZK_BMW], m_stat[ZK_BMW];
 	uint32_t sub0[ZK_BMW], sub1[ZK_BMW];
@@ -1559,17 +1563,20 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 #endif
 }
 
-/* One CTA = ZK_DEC_WARPS warps = that many consecutive chunks.  Chunks are handed out in
- * launch order through one ticket per CTA, so every chunk a warp may wait for in the
- * look-back belongs to a CTA that is already running: no deadlock whatever order the
- * hardware starts CTAs in.  (Measured alternatives: a ticket per warp, and persistent warps
- * that loop over tickets, were both slower — see profiles/r1_notes.md.)  After the ticket
- * the warps never wait for each other except through the look-back. */
-__global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
+/* One CTA = ZK_DEC_WARPS warps = that many consecutive chunks, chunk index from blockIdx.
+ * The look-back only ever waits for chunks of lower-numbered CTAs; like CUB's single-pass
+ * scan this relies on the hardware starting CTAs in index order (it does), and the spin
+ * limit in the look-back turns any violation into an error instead of a hang.  (Measured
+ * alternatives — an atomic ticket per warp or per CTA, persistent warps looping over
+ * tickets, 4 KiB chunks at higher occupancy — were all slower: profiles/r1_notes.md.)
+ * The warps of a CTA never wait for each other. */
+#ifndef ZK_DEC_MINBLOCKS
+#define ZK_DEC_MINBLOCKS 5
+#endif
+__global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(DecArgs a)
 {
 	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
 	__shared__ __align__(8) uint64_t s_bar[ZK_DEC_WARPS];
-	__shared__ uint32_t s_ticket;
 	const uint32_t lane = threadIdx.x & 31;
 	ChunkSm &c = sm_all[threadIdx.x >> 5];
 	uint64_t *bar = &s_bar[threadIdx.x >> 5];
@@ -1578,11 +1585,10 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, 5) k_decode(DecArgs a)
 #else
 	const long long t0 = 0;
 #endif
-	if (lane == 0) mbar_init(bar, 1);
-	if (threadIdx.x == 0) s_ticket = atomicAdd(&a.ctrl->ticket, 1u);
-	__syncthreads();
-	const uint32_t chunk = s_ticket * ZK_DEC_WARPS + (threadIdx.x >> 5);
+	const uint32_t chunk = blockIdx.x * ZK_DEC_WARPS + (threadIdx.x >> 5);
 	if (chunk >= a.n_chunks) return;
+	if (lane == 0) mbar_init(bar, 1);
+	__syncwarp();
 	decode_chunk(a, c, bar, 0, chunk, lane, t0);
 }
 
@@ -1624,7 +1630,7 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 	/* aim for ~256K granules so the splitter has enough threads, within [1 KiB, 32 KiB] */
 	uint64_t want = (nbytes + 262143) / 262144;
 	uint32_t l = ZK_GRAN_MIN_LOG2;
-	while (l < ZK_GRAN_MAX_LOG2 && (1ull << l) < want) l++;
+	while (l < ZK_GRAN_MAX_LOG2 && l < ZK_CHUNK_LOG2 && (1ull << l) < want) l++;
 	return l;
 }
 
