@@ -106,6 +106,10 @@ extern "C" __attribute__((visibility("default"))) void zkb_debug_phase_cycles(co
 {
 	memcpy(out, ctx->prof, sizeof (ctx->prof));
 }
+extern "C" __attribute__((visibility("default"))) void zkb_debug_split_cycles(const zkb_ctx *ctx, unsigned long long out[8])
+{
+	memcpy(out, ctx->split_prof, sizeof (ctx->split_prof));
+}
 #endif
 ZKB_EXPORT int zkb_ctx_set_timing(zkb_ctx *ctx, int on)
 {

@@ -348,6 +348,9 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 	const bool last = (g == a.n_gran - 1);
 	const uint64_t ge = last ? a.nbytes : gs + (1ull << a.glog2);
 
+#ifdef ZK_PROFILE_PHASES
+	const long long sp_t0 = clock64();
+#endif
 	uint32_t sf = lower_bound_u64(a.sess_off, a.nsess + 1, gs);
 	if (sf > a.nsess) return;   /* offsets do not cover the batch: k_check_sessions reports it */
 	bool cont = (__ldg(a.sess_off + sf) != gs);   /* granule starts inside session sf-1 */
@@ -362,6 +365,9 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		assumed = (MODE == MODE_SPEC) ? guess_entry(a, s, gs, ge, send) : a.g_carry[g];
 	}
 	if (MODE == MODE_SPEC) __syncwarp();   /* lanes finish guessing at different times: walk together */
+#ifdef ZK_PROFILE_PHASES
+	const long long sp_t1 = clock64();
+#endif
 	if (cont) {
 		uint32_t s = sf - 1;
 		uint64_t send = __ldg(a.sess_off + sf);
@@ -378,6 +384,17 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		pos = walk_chain<MODE>(a, s, so, __ldg(a.sess_off + s + 1), ge, count, base);
 	}
 	const uint64_t out = touched ? pos : ZK_INHERIT;
+#ifdef ZK_PROFILE_PHASES
+	if (MODE == MODE_SPEC) {
+		__syncwarp();
+		const long long sp_t2 = clock64();
+		if ((threadIdx.x & 31) == 0) {
+			atomicAdd(&a.ctrl->prof[0], (unsigned long long)(sp_t1 - sp_t0));
+			atomicAdd(&a.ctrl->prof[1], (unsigned long long)(sp_t2 - sp_t1));
+			atomicAdd(&a.ctrl->prof[2], 1ull);
+		}
+	}
+#endif
 	if (MODE == MODE_EMIT) {
 		if (count != a.g_cnt[(size_t)a.g_sel[g] * a.n_gran + g]) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
 	} else if (MODE == MODE_SPEC) {
@@ -1772,6 +1789,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		}
 	}
 	*n_frames = ctx->h_ctrl->n_frames;
+	memcpy(ctx->split_prof, ctx->h_ctrl->prof, sizeof (ctx->split_prof));
 	return ZKB_OK;
 }
 

@@ -50,6 +50,7 @@ struct zkb_ctx {
 	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
 	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
 	unsigned long long prof[8];
+	unsigned long long split_prof[8];
 	/* device scratch (grown on demand, never shrunk) */
 	void         *d_scratch;   size_t d_scratch_bytes;
 	zk_ctrl      *d_ctrl;

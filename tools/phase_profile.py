@@ -30,6 +30,12 @@ for label, data, off, fl, xt in (("request streams", pc.req, pc.req_off, pc.req_
     dc = dev.decode_dev_autosize(ctx, d, int(data.size), ds, dx, device=device)
     for _ in range(3):
         dev.decode_dev(ctx, d, int(data.size), ds, dx, dc)
+    sp = (C.c_ulonglong * 8)()
+    lib.zkb_debug_split_cycles.argtypes = [C.c_void_p, C.POINTER(C.c_ulonglong * 8)]
+    lib.zkb_debug_split_cycles(ctx._h, C.byref(sp))
+    if sp[2]:
+        print(label, "k_split<SPEC> per warp: guess %.0f cycles, walk %.0f cycles (%d warps)" % (
+            sp[0] / sp[2], sp[1] / sp[2], sp[2]))
     out = (C.c_ulonglong * 8)()
     lib.zkb_debug_phase_cycles(ctx._h, C.byref(out))
     n = max(1, out[7])
