@@ -41,8 +41,8 @@ METRIC = "decoded_zk_frames_per_sec"
 UNIT = "frames/s"
 FRAMES_PER_SESSION = 20000
 BYTES_PER_SESSION = 7.79e6          # request + response stream of one session (measured)
-# bytes k_decode writes per row: FRAMES (meta, xid, zxid, err, a0, a1), STAT, BUF, ACL
-ROW_BYTES = {"frames_decode": 28, "frames_emit": 16, "stat": 72, "buf": 16, "acl": 8}
+# bytes k_decode writes per row: FRAMES (all nine columns, 44 B), STAT, BUF, ACL
+ROW_BYTES = {"frames_decode": 44, "frames_emit": 0, "stat": 72, "buf": 16, "acl": 8}
 
 
 def env_int(name, default):

@@ -106,7 +106,7 @@ __device__ __forceinline__ void st_desc(uint4 *p, uint4 v)
 /* ================================================================================== */
 /* splitter                                                                           */
 
-enum { MODE_SPEC = 0, MODE_FIX = 1, MODE_EMIT = 2 };
+enum { MODE_SPEC = 0, MODE_FIX = 1 };
 
 struct SplitArgs {
 	const uint8_t  *bytes;
@@ -127,14 +127,12 @@ struct SplitArgs {
 	uint32_t       *g_base;      /* exclusive prefix of g_cnt */
 	uint8_t        *g_dirty;
 	uint32_t       *g_src;       /* 1 + index of the granule whose exit is this granule's carry; 0 = none */
-	/* EMIT */
-	uint64_t       *frame_off;
-	int32_t        *frame_len;
-	uint32_t       *session;
-	uint64_t        cap_frames;
-	uint64_t       *sess_consumed;
-	uint64_t       *sess_bad;
-	uint32_t       *sess_first;
+	uint32_t       *g_sf;        /* first session that starts at or after the granule's first byte */
+	uint32_t       *g_openlocal; /* [version][g]: frames of the granule before the first frame of the
+	                                last session that starts inside it (valid if one does) */
+	uint32_t       *g_ssrc;      /* 1 + index of the last granule before this one in which a session starts */
+	uint16_t       *g_sub;       /* [version][g][granule/256]: where the chain first stands inside each
+	                                256-byte sub-range (offset from the granule start), 0xFFFF = nowhere */
 	zk_ctrl        *ctrl;
 };
 
@@ -296,43 +294,25 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 }
 
 /* The loop of ZKDecodeStream._transform (zk-streams.js:47-64) restricted to the frames
- * that start before `ge`.  Returns where the chain stands afterwards. */
-template <int MODE>
-__device__ uint64_t walk_chain(const SplitArgs &a, uint32_t s, uint64_t pos, uint64_t send,
-    uint64_t ge, uint32_t &count, uint32_t base)
+ * that start before `ge`: counts them and returns where the chain stands afterwards
+ * (ZK_NONE once the session's chain has ended: stream exhausted, frame incomplete, or
+ * BAD_LENGTH).  The decode kernel repeats this walk on the staged bytes to place frames. */
+__device__ uint64_t walk_chain(const SplitArgs &a, uint64_t pos, uint64_t send, uint64_t ge, uint32_t &count,
+    uint64_t gs, uint16_t *row, uint32_t &last_sub)
 {
 	for (;;) {
-		uint64_t bad = ZK_NONE;
-		bool stop = false;
-		int32_t len = 0;
-		if (pos == send) {
-			stop = true;
-		} else {
-			if (pos >= ge) return pos;
-			uint64_t rem = send - pos;
-			if (rem < 4) {
-				stop = true;                                /* zd_used < 4 */
-			} else {
-				len = (int32_t)g_be32(a.bytes, pos);
-				if (!len_ok(len)) { stop = true; bad = pos; } /* :49-53 BAD_LENGTH */
-				else if (rem < 4 + (uint64_t)len) stop = true;   /* frame not complete yet */
-			}
+		if (pos < ge) {
+			/* positions only grow, so each sub-range is recorded at most once */
+			const uint32_t idx = (uint32_t)(pos - gs) >> 8;
+			if (idx != last_sub) { row[idx] = (uint16_t)(pos - gs); last_sub = idx; }
 		}
-		if (stop) {
-			if (MODE == MODE_EMIT) {
-				a.sess_consumed[s] = pos;
-				a.sess_bad[s] = bad;
-			}
-			return ZK_NONE;
-		}
-		if (MODE == MODE_EMIT) {
-			uint64_t row = (uint64_t)base + count;
-			if (row < a.cap_frames) {
-				a.frame_off[row] = pos;
-				a.frame_len[row] = len;
-				a.session[row] = s;
-			}
-		}
+		if (pos == send) return ZK_NONE;
+		if (pos >= ge) return pos;
+		const uint64_t rem = send - pos;
+		if (rem < 4) return ZK_NONE;                        /* zd_used < 4 */
+		const int32_t len = (int32_t)g_be32(a.bytes, pos);
+		if (!len_ok(len)) return ZK_NONE;                   /* :49-53 BAD_LENGTH */
+		if (rem < 4 + (uint64_t)len) return ZK_NONE;        /* frame not complete yet */
 		count++;
 		pos += 4 + (uint64_t)len;
 	}
@@ -351,13 +331,12 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 #ifdef ZK_PROFILE_PHASES
 	const long long sp_t0 = clock64();
 #endif
-	uint32_t sf = lower_bound_u64(a.sess_off, a.nsess + 1, gs);
+	uint32_t sf = (MODE == MODE_SPEC) ? lower_bound_u64(a.sess_off, a.nsess + 1, gs) : a.g_sf[g];
 	if (sf > a.nsess) return;   /* offsets do not cover the batch: k_check_sessions reports it */
 	bool cont = (__ldg(a.sess_off + sf) != gs);   /* granule starts inside session sf-1 */
 	uint64_t assumed = ZK_NONE, pos = ZK_NONE;
-	uint32_t count = 0;
-	bool touched = false;
-	const uint32_t base = (MODE == MODE_EMIT) ? a.g_base[g] : 0;
+	uint32_t count = 0, open_local = 0;
+	bool touched = false, has_start = false;
 
 	if (cont) {
 		uint32_t s = sf - 1;
@@ -368,20 +347,31 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 #ifdef ZK_PROFILE_PHASES
 	const long long sp_t1 = clock64();
 #endif
+	/* this walk's row of sub-range entries: version 0 (and 1, copied below) in SPEC, version 1 in FIX */
+	const uint32_t subs = 1u << (a.glog2 - 8);
+	uint16_t *row = a.g_sub + ((size_t)(MODE == MODE_SPEC ? 0 : a.n_gran) + g) * subs;
+	for (uint32_t i = 0; i < subs; i += 8)
+		*reinterpret_cast<uint4 *>(row + i) = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+	uint32_t last_sub = 0xFFFFFFFFu;
 	if (cont) {
-		uint32_t s = sf - 1;
 		uint64_t send = __ldg(a.sess_off + sf);
 		if (assumed >= gs && assumed < ge) {
 			touched = true;
-			pos = walk_chain<MODE>(a, s, assumed, send, ge, count, base);
+			pos = walk_chain(a, assumed, send, ge, count, gs, row, last_sub);
 		}
 	}
 	for (uint32_t s = sf; s < a.nsess; ++s) {
 		uint64_t so = __ldg(a.sess_off + s);
 		if (!(so < ge || last)) break;
 		touched = true;
-		if (MODE == MODE_EMIT) a.sess_first[s] = base + count;
-		pos = walk_chain<MODE>(a, s, so, __ldg(a.sess_off + s + 1), ge, count, base);
+		has_start = true;
+		open_local = count;
+		pos = walk_chain(a, so, __ldg(a.sess_off + s + 1), ge, count, gs, row, last_sub);
+	}
+	if (MODE == MODE_SPEC) {
+		uint16_t *row1 = a.g_sub + ((size_t)a.n_gran + g) * subs;
+		for (uint32_t i = 0; i < subs; i += 8)
+			*reinterpret_cast<uint4 *>(row1 + i) = *reinterpret_cast<const uint4 *>(row + i);
 	}
 	const uint64_t out = touched ? pos : ZK_INHERIT;
 #ifdef ZK_PROFILE_PHASES
@@ -395,12 +385,13 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		}
 	}
 #endif
-	if (MODE == MODE_EMIT) {
-		if (count != a.g_cnt[(size_t)a.g_sel[g] * a.n_gran + g]) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
-	} else if (MODE == MODE_SPEC) {
-		a.g_assumed[g] = assumed; a.g_out[g] = out; a.g_cnt[g] = count;
+	if (MODE == MODE_SPEC) {
+		a.g_assumed[g] = assumed; a.g_out[g] = out; a.g_cnt[g] = count; a.g_openlocal[g] = open_local;
 		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = out; a.g_cnt[a.n_gran + g] = count;
+		a.g_openlocal[a.n_gran + g] = open_local;
 		a.g_sel[g] = 0;
+		a.g_sf[g] = sf;
+		(void)has_start;
 	} else {
 		/* Every dirty granule re-walks from its carried position, but the result only
 		 * replaces the guess-based one in the next scan if that position can be trusted:
@@ -410,6 +401,7 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		 * cannot push an error wave down the stream.  The lowest dirty granule always
 		 * qualifies, so every iteration makes progress. */
 		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = out; a.g_cnt[a.n_gran + g] = count;
+		a.g_openlocal[a.n_gran + g] = open_local;
 		const uint32_t src = a.g_src[g];
 		const bool trusted = !(src && a.g_dirty[src - 1]) && !(assumed != ZK_NONE && assumed < gs);
 		a.g_sel[g] = trusted ? 1 : 0;
@@ -418,14 +410,16 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 
 /* ---- scan over granules: value = (last exit that is not INHERIT, sum of counts) ------ */
 
-struct ScanVal { uint64_t v; uint32_t c; uint32_t src; };
+struct ScanVal { uint64_t v; uint32_t c; uint32_t src; uint32_t ssrc; uint32_t pad; };
 
 __device__ __forceinline__ ScanVal sv_comb(ScanVal l, ScanVal r)
 {
 	ScanVal o;
 	o.v = (r.v != ZK_INHERIT) ? r.v : l.v;
 	o.src = (r.v != ZK_INHERIT) ? r.src : l.src;
+	o.ssrc = r.ssrc ? r.ssrc : l.ssrc;
 	o.c = l.c + r.c;
+	o.pad = 0;
 	return o;
 }
 __device__ __forceinline__ ScanVal sv_shfl_up(ScanVal x, int d)
@@ -434,6 +428,8 @@ __device__ __forceinline__ ScanVal sv_shfl_up(ScanVal x, int d)
 	o.v = __shfl_up_sync(0xffffffffu, x.v, d);
 	o.c = __shfl_up_sync(0xffffffffu, x.c, d);
 	o.src = __shfl_up_sync(0xffffffffu, x.src, d);
+	o.ssrc = __shfl_up_sync(0xffffffffu, x.ssrc, d);
+	o.pad = 0;
 	return o;
 }
 
@@ -449,7 +445,7 @@ __device__ ScanVal block_scan_incl(ScanVal x, ScanVal *total, ScanVal *s_w /* [3
 	}
 	if (lane == 31) s_w[wid] = x;
 	__syncthreads();
-	ScanVal pre; pre.v = ZK_INHERIT; pre.c = 0; pre.src = 0;
+	ScanVal pre; pre.v = ZK_INHERIT; pre.c = 0; pre.src = 0; pre.ssrc = 0; pre.pad = 0;
 	ScanVal tot = pre;
 	const int nw = blockDim.x >> 5;
 	for (int w = 0; w < nw; ++w) {
@@ -465,10 +461,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 {
 	__shared__ ScanVal s_w[32];
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
-	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0;
+	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.pad = 0;
 	if (g < a.n_gran) {
 		const size_t i = (size_t)a.g_sel[g] * a.n_gran + g;
 		x.v = a.g_out[i]; x.c = a.g_cnt[i]; x.src = g + 1;
+		const uint32_t sf = a.g_sf[g];
+		const uint64_t gend = (g == a.n_gran - 1) ? a.nbytes + 1 : ((uint64_t)(g + 1) << a.glog2);
+		x.ssrc = (sf < a.nsess && __ldg(a.sess_off + sf) < gend) ? g + 1 : 0;
 	}
 	ScanVal tot;
 	block_scan_incl(x, &tot, s_w);
@@ -479,10 +478,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint32_t nblk)
 {
 	__shared__ ScanVal s_w[32];
-	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.src = 0;
+	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.src = 0; carry.ssrc = 0; carry.pad = 0;
 	for (uint32_t b0 = 0; b0 < nblk; b0 += SCAN_THREADS) {
 		uint32_t i = b0 + threadIdx.x;
-		ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0;
+		ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.pad = 0;
 		if (i < nblk) x = blk[i];
 		ScanVal tot;
 		ScanVal inc = block_scan_incl(x, &tot, s_w);
@@ -492,7 +491,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint
 		if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
 		__syncthreads();
 		ScanVal ex;
-		if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; }
+		if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; ex.ssrc = 0; ex.pad = 0; }
 		else if ((threadIdx.x & 31) == 0) ex = s_last[(threadIdx.x >> 5) - 1];
 		else ex = prev;
 		if (i < nblk) blk[i] = sv_comb(carry, ex);
@@ -506,10 +505,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	__shared__ ScanVal s_w[32];
 	__shared__ ScanVal s_last[32];
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
-	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0;
+	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.pad = 0;
 	if (g < a.n_gran) {
 		const size_t i = (size_t)a.g_sel[g] * a.n_gran + g;
 		x.v = a.g_out[i]; x.c = a.g_cnt[i]; x.src = g + 1;
+		const uint32_t sf = a.g_sf[g];
+		const uint64_t gend = (g == a.n_gran - 1) ? a.nbytes + 1 : ((uint64_t)(g + 1) << a.glog2);
+		x.ssrc = (sf < a.nsess && __ldg(a.sess_off + sf) < gend) ? g + 1 : 0;
 	}
 	ScanVal tot;
 	ScanVal inc = block_scan_incl(x, &tot, s_w);
@@ -517,7 +519,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
 	__syncthreads();
 	ScanVal ex;
-	if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; }
+	if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; ex.ssrc = 0; ex.pad = 0; }
 	else if ((threadIdx.x & 31) == 0) ex = s_last[(threadIdx.x >> 5) - 1];
 	else ex = prev;
 	ex = sv_comb(blk[blockIdx.x], ex);
@@ -528,6 +530,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	a.g_carry[g] = carry;
 	a.g_base[g] = ex.c;
 	a.g_src[g] = (ex.v == ZK_INHERIT) ? 0u : ex.src;
+	a.g_ssrc[g] = ex.ssrc;
 	/* a walk is consistent with the carry iff both name the same in-granule position, or
 	 * neither names one; pick whichever version is, else the granule is dirty */
 	const uint64_t nc = (carry >= gs && carry < ge) ? carry : ZK_NONE;
@@ -581,7 +584,15 @@ struct DecArgs {
 	const uint32_t *xt_count;
 	const uint64_t *xt_off;
 	const int8_t   *xt_ops;
-	const uint32_t *g_base;
+	const uint64_t *sess_off;
+	uint32_t        nsess;
+	const uint32_t *g_base;       /* per granule: first frame index */
+	const uint64_t *g_carry;      /* per granule: where the chain stands on entry */
+	const uint32_t *g_sf;         /* per granule: first session starting at or after it */
+	const uint32_t *g_ssrc;       /* per granule: 1 + last earlier granule with a session start */
+	const uint32_t *g_openlocal;  /* [version][g] */
+	const uint16_t *g_sub;        /* [version][g][granule/256] chain entry per 256-byte sub-range */
+	const uint8_t  *g_sel;
 	uint32_t        glog2;
 	uint32_t        n_gran;
 	uint32_t        n_chunks;
@@ -1316,11 +1327,9 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	const uint32_t wlen = avail < (uint64_t)ZK_WIN ? (uint32_t)avail : ZK_WIN;
 
 	/* ---- stage the chunk: one TMA bulk copy (global -> shared, completion on an mbarrier)
-	 * issued by lane 0; while it is in flight the warp clears its bitmaps and fetches the
-	 * chunk's frame range and first frame rows, so those round trips overlap the copy ---- */
+	 * issued by lane 0; while it is in flight the warp clears its bitmaps and fetches what
+	 * the splitter's scan says about the chunk, so those round trips overlap the copy ---- */
 	if (lane == 0) {
-		/* the previous chunk's reads of this tile (generic proxy) are done: order them before
-		 * the async-proxy write that refills it */
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 		mbar_expect_tx(bar, wlen);
 		bulk_g2s(c.tile, a.bytes + cs, wlen, bar);
@@ -1337,36 +1346,201 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	const uint32_t f0 = a.g_base[g0];
 	const uint32_t f1 = (g1 < a.n_gran) ? a.g_base[g1] : (uint32_t)a.n_frames;
 	const uint32_t nfr = f1 - f0;
-	/* first round's rows, fetched before the tile has landed */
-	uint64_t pf_off = 0; int32_t pf_len = 0; uint32_t pf_s = 0;
-	if (lane < nfr) {
-		pf_off = a.o.frame_off[f0 + lane];
-		pf_len = a.o.frame_len[f0 + lane];
-		pf_s = a.o.session[f0 + lane];
+	const bool last = (chunk == a.n_chunks - 1);
+	const uint64_t ce = last ? a.nbytes : cs + ZK_CHUNK;
+	const uint32_t sf = a.g_sf[g0];                  /* first session starting at or after cs */
+	/* session boundaries from sf on, one per lane: boff[l] = sess_off[sf + l] */
+	uint64_t boff = ZK_NONE;
+	if (sf + lane <= a.nsess) boff = __ldg(a.sess_off + sf + lane);
+	const uint64_t boff0 = __shfl_sync(0xffffffffu, boff, 0);
+	const bool cont = (boff0 != cs);                 /* the chunk starts inside session sf-1 */
+	/* first frame (global row) of the session the chunk starts in, from the splitter's scan */
+	uint32_t sfirst = 0;
+	if (cont) {
+		const uint32_t src = a.g_ssrc[g0];
+		if (src) sfirst = a.g_base[src - 1] + a.g_openlocal[(size_t)a.g_sel[src - 1] * a.n_gran + (src - 1)];
+	}
+	/* where the chain stands inside this lane's 256-byte sub-range, from the splitter */
+	const uint64_t lo = cs + 256u * lane;
+	const uint64_t hi = (lo + 256 < ce) ? lo + 256 : ce;
+	uint64_t entry = ZK_NONE;
+	if (lo < ce) {
+		const uint32_t g = (uint32_t)(lo >> a.glog2);
+		const uint64_t gstart = (uint64_t)g << a.glog2;
+		const uint32_t subs = 1u << (a.glog2 - 8);
+		const uint16_t v = a.g_sub[((size_t)a.g_sel[g] * a.n_gran + g) * subs + (uint32_t)((lo - gstart) >> 8)];
+		if (v != 0xFFFFu) entry = gstart + v;
 	}
 	__syncwarp();
 	ZK_T(2);
 	mbar_wait(bar, phase);
 	ZK_T(3);
 
-	/* ---- frames: lane k handles frames f0+k, f0+k+32, ... ---- */
+	/* ---- frame starts: every lane repeats the loop of ZKDecodeStream._transform
+	 * (zk-streams.js:47-64) on its own 256 bytes of the staged chunk, from where the splitter
+	 * says the chain stands there; it marks frame starts in `fstart` (+ low position bits in
+	 * sub0/sub1; a lane owns the two bitmap words of its sub-range) and writes the result of
+	 * every session that ends under its hands ---- */
+	{
+		/* session context of the entry: jl = boundaries sess_off[sf + l], l < 32, strictly below it */
+		const uint64_t e = (entry != ZK_NONE) ? entry : 0;
+		uint32_t jl = 0;
+#pragma unroll
+		for (int step = 16; step > 0; step >>= 1) {
+			const uint64_t bv = __shfl_sync(0xffffffffu, boff, (int)(jl + step - 1));
+			if (bv < e) jl += step;
+		}
+		{
+			const uint64_t bv = __shfl_sync(0xffffffffu, boff, 31);
+			if (jl == 31 && bv < e) jl = 32;
+		}
+		uint64_t b_at = __shfl_sync(0xffffffffu, boff, (int)(jl < 32 ? jl : 31));       /* sess_off[sf + jl] */
+		uint64_t b_next = __shfl_sync(0xffffffffu, boff, (int)(jl + 1 < 32 ? jl + 1 : 31)); /* sess_off[sf + jl + 1] */
+		uint32_t cnt = 0;
+		if (entry != ZK_NONE) {
+			uint32_t sprev = sf - 1 + jl;          /* last session that starts strictly before the entry */
+			if (jl >= 32) {                        /* > 32 session starts in this chunk: use the table */
+				uint32_t l2 = sf + 31, h2 = a.nsess;
+				while (h2 - l2 > 1) {
+					const uint32_t mid = (l2 + h2) >> 1;
+					if (__ldg(a.sess_off + mid) < entry) l2 = mid; else h2 = mid;
+				}
+				sprev = l2;
+				b_at = __ldg(a.sess_off + sprev + 1);
+			}
+			if (jl + 1 >= 32 || jl >= 32) b_next = (sprev + 2 <= a.nsess) ? __ldg(a.sess_off + sprev + 2) : ZK_NONE;
+			uint32_t s; uint64_t pos = entry, send;
+			if (entry < b_at) { s = sprev; send = b_at; }          /* inside session sprev */
+			else { s = sprev + 1; send = b_next; }                 /* the entry is where session sprev+1 starts */
+			for (;;) {
+				uint64_t bad = ZK_NONE;
+				bool stop = false;
+				for (;;) {
+					if (pos == send) { stop = true; break; }
+					if (pos >= hi) break;
+					const uint64_t rem = send - pos;
+					if (rem < 4) { stop = true; break; }                      /* zd_used < 4 */
+					const uint32_t rel = (uint32_t)(pos - cs);
+					const int32_t len = (int32_t)sm_be32(c.tile, rel);
+					if (!len_ok(len)) { stop = true; bad = pos; break; }      /* :49-53 BAD_LENGTH */
+					if (rem < 4 + (uint64_t)len) { stop = true; break; }      /* frame not complete yet */
+					const uint32_t w = rel >> 7, bit = 1u << ((rel >> 2) & 31);
+					c.fstart[w] |= bit;
+					if (rel & 1) c.sub0[w] |= bit;
+					if (rel & 2) c.sub1[w] |= bit;
+					cnt++;
+					pos += 4 + (uint64_t)len;
+				}
+				if (!stop) break;                 /* the chain leaves the sub-range alive */
+				a.o.sess_consumed[s] = pos;
+				a.o.sess_bad_length_at[s] = bad;
+				/* next session, if it starts inside this sub-range */
+				if (s + 1 >= a.nsess) break;
+				const uint64_t so = send;
+				if (!(so < hi)) break;
+				s++;
+				pos = so;
+				send = __ldg(a.sess_off + s + 1);
+			}
+		}
+		cnt = warp_sum(cnt);
+		if (lane == 0 && cnt != nfr) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
+		/* empty sessions at the very end of the batch start at nbytes, in no sub-range */
+		if (last && lane == 0) {
+			for (uint32_t sx = a.nsess; sx > 0 && __ldg(a.sess_off + sx - 1) == a.nbytes; --sx) {
+				a.o.sess_consumed[sx - 1] = a.nbytes;
+				a.o.sess_bad_length_at[sx - 1] = ZK_NONE;
+			}
+		}
+	}
+	__syncwarp();
+	/* exclusive prefix of frame starts per bitmap word */
+	{
+		uint32_t run = 0;
+		for (uint32_t w0 = 0; w0 < ZK_BMW; w0 += 32) {
+			const uint32_t w = w0 + lane;
+			const uint32_t fc = (w < ZK_BMW) ? __popc(c.fstart[w]) : 0u;
+			const uint32_t inc = warp_incl_scan(fc, lane);
+			if (w < ZK_BMW) c.fpre[w] = (uint16_t)(run + inc - fc);
+			run += __shfl_sync(0xffffffffu, inc, 31);
+		}
+	}
+	__syncwarp();
+	/* rows before byte `relpos` of the chunk = frames that start below it */
+	auto rank_below = [&](uint32_t relpos) -> uint32_t {
+		if (relpos >= ZK_SLOTS * 4u) return nfr;
+		const uint32_t w = relpos >> 7, b = (relpos >> 2) & 31;
+		return (uint32_t)c.fpre[w] + __popc(c.fstart[w] & ((1u << b) - 1));
+	};
+	/* sess_first_frame for every session that starts inside the chunk (empty ones included) */
+	for (uint32_t q = lane;; q += 32) {
+		const uint32_t sq = sf + q;
+		if (sq >= a.nsess) break;
+		const uint64_t so = (q < 32) ? boff : __ldg(a.sess_off + sq);
+		if (!(so < ce || last)) break;
+		a.o.sess_first_frame[sq] = f0 + rank_below((uint32_t)(so - cs));
+	}
+	const bool one_session = cont && !(boff0 < ce || (last && sf < a.nsess));   /* no session starts inside */
+
+	/* ---- frames: lane k takes the k-th, (k+32)-th ... frame start of the chunk ---- */
 	Parsed lp;                       /* the chunk's long frame (reaches past the tile), if this lane has it */
 	uint64_t l_foff = 0; int32_t l_flen = 0; uint32_t l_f = 0;
 	lp.n_stat = lp.n_buf = lp.n_acl = 0;
 	uint32_t n_slow = 0;
 	for (uint32_t k0 = 0; k0 < nfr; k0 += 32) {
 		const uint32_t k = k0 + lane;
-		if (k >= nfr) continue;
+		const bool valid = k < nfr;
+		uint32_t rel = 0;
+		if (valid) {
+			/* word that holds the k-th frame start: last w with fpre[w] <= k */
+			uint32_t lo = 0, hi = ZK_BMW;
+			while (hi - lo > 1) {
+				const uint32_t mid = (lo + hi) >> 1;
+				if ((uint32_t)c.fpre[mid] <= k) lo = mid; else hi = mid;
+			}
+			const uint32_t b = __fns(c.fstart[lo], 0, (int)(k - c.fpre[lo]) + 1);
+			rel = ((lo * 32 + b) << 2) | ((c.sub0[lo] >> b) & 1) | (((c.sub1[lo] >> b) & 1) << 1);
+		}
 		const uint32_t f = f0 + k;
-		const uint64_t foff = k0 ? a.o.frame_off[f] : pf_off;
-		const int32_t flen = k0 ? a.o.frame_len[f] : pf_len;
-		const uint32_t s = k0 ? a.o.session[f] : pf_s;
-		const uint32_t rel = (uint32_t)(foff - cs);
-		atomicOr(&c.fstart[rel >> 7], 1u << ((rel >> 2) & 31));
+		const uint64_t foff = cs + rel;
+		const int32_t flen = valid ? (int32_t)sm_be32(c.tile, rel) : 0;
+		/* which session, and where that session's frames begin */
+		uint32_t s = sf - 1, first = sfirst;
+		if (!one_session) {
+			/* j = number of boundaries sess_off[sf + l], l < 32, at or below the frame */
+			uint32_t j = 0;
+#pragma unroll
+			for (int step = 16; step > 0; step >>= 1) {
+				const uint64_t bv = __shfl_sync(0xffffffffu, boff, (int)(j + step - 1));
+				if (bv <= foff) j += step;
+			}
+			{
+				const uint64_t bv = __shfl_sync(0xffffffffu, boff, 31);
+				if (j == 31 && bv <= foff) j = 32;
+			}
+			uint64_t so = __shfl_sync(0xffffffffu, boff, (int)(j ? j - 1 : 0));
+			if (j == 32 && valid) {
+				/* more than 32 sessions start in this chunk before the frame: search the table */
+				uint32_t lo = sf + 31, hi = a.nsess;          /* last s with sess_off[s] <= foff */
+				while (hi - lo > 1) {
+					const uint32_t mid = (lo + hi) >> 1;
+					if (__ldg(a.sess_off + mid) <= foff) lo = mid; else hi = mid;
+				}
+				s = lo; so = __ldg(a.sess_off + lo);
+				first = f0 + rank_below((uint32_t)(so - cs));
+			} else if (j) {
+				s = sf + j - 1;
+				first = f0 + rank_below((uint32_t)(so - cs));
+			}
+		}
+		if (!valid) continue;
+		a.o.frame_off[f] = foff;
+		a.o.frame_len[f] = flen;
+		a.o.session[f] = s;
 		const bool inwin = rel + 4u + (uint32_t)flen <= wlen;
 		const bool server = a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER);
 		const uint32_t hs = a.sess_hs ? __ldg(a.sess_hs + s) : 1u;
-		const uint32_t idx = f - __ldg(a.o.sess_first_frame + s);
+		const uint32_t idx = f - first;
 		FrameCols o;
 		int done = -1;
 		if (inwin && idx >= hs) {
@@ -1403,21 +1577,10 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	n_slow = warp_sum(n_slow);
 	if (lane == 0 && n_slow) atomicAdd(&a.ctrl->n_slow, (unsigned long long)n_slow);
 
-	/* ---- row counts of this chunk; prefix of frame-start bits per bitmap word ---- */
+	/* ---- side-table row counts of this chunk ---- */
 	uint32_t nb = 0, na = 0, ns = 0;
-	{
-		uint32_t run = 0;
-		for (uint32_t w0 = 0; w0 < ZK_BMW; w0 += 32) {
-			const uint32_t w = w0 + lane;
-			uint32_t fc = 0;
-			if (w < ZK_BMW) {
-				nb += __popc(c.m_buf[w]); na += __popc(c.m_acl[w]); ns += __popc(c.m_stat[w]);
-				fc = __popc(c.fstart[w]);
-			}
-			const uint32_t inc = warp_incl_scan(fc, lane);
-			if (w < ZK_BMW) c.fpre[w] = (uint16_t)(run + inc - fc);
-			run += __shfl_sync(0xffffffffu, inc, 31);
-		}
+	for (uint32_t w = lane; w < ZK_BMW; w += 32) {
+		nb += __popc(c.m_buf[w]); na += __popc(c.m_acl[w]); ns += __popc(c.m_stat[w]);
 	}
 	nb = warp_sum(nb); na = warp_sum(na); ns = warp_sum(ns);
 	const uint32_t tb = nb + warp_sum(lp.n_buf), ta = na + warp_sum(lp.n_acl), ts = ns + warp_sum(lp.n_stat);
@@ -1652,7 +1815,7 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 }
 
 struct ScratchLayout {
-	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, blk, lb, total;
+	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, blk, lb, total;
 	uint32_t glog2, n_gran, n_chunks, n_blk;
 };
 
@@ -1673,6 +1836,10 @@ static ScratchLayout zk_layout(uint64_t nbytes)
 	L.g_base = o;    o += zk_align_up((size_t)(L.n_gran + 1) * 4, 256);
 	L.g_dirty = o;   o += zk_align_up((size_t)L.n_gran, 256);
 	L.g_src = o;     o += zk_align_up((size_t)L.n_gran * 4, 256);
+	L.g_sf = o;      o += zk_align_up((size_t)L.n_gran * 4, 256);
+	L.g_openlocal = o; o += zk_align_up((size_t)L.n_gran * 8, 256);
+	L.g_ssrc = o;    o += zk_align_up((size_t)L.n_gran * 4, 256);
+	L.g_sub = o;     o += zk_align_up((size_t)L.n_gran * 2 * ((size_t)1 << (L.glog2 - 8)) * 2, 256);
 	L.blk = o;       o += zk_align_up((size_t)(L.n_blk + 1) * sizeof (ScanVal), 256);
 	L.lb = o;        o += zk_align_up((size_t)L.n_chunks * 16, 256);
 	L.total = o;
@@ -1700,7 +1867,7 @@ static int zk_read_ctrl(zkb_ctx *ctx)
 	} while (0)
 
 static int zk_fill_split_args(zkb_ctx *ctx, SplitArgs &sa, const ScratchLayout &L,
-    const uint8_t *d_bytes, uint64_t nbytes, const zkb_sessions *sess, const zkb_decoded *out)
+    const uint8_t *d_bytes, uint64_t nbytes, const zkb_sessions *sess)
 {
 	uint8_t *S = (uint8_t *)ctx->d_scratch;
 	memset(&sa, 0, sizeof (sa));
@@ -1710,12 +1877,8 @@ static int zk_fill_split_args(zkb_ctx *ctx, SplitArgs &sa, const ScratchLayout &
 	sa.g_carry = (uint64_t *)(S + L.g_carry); sa.g_cnt = (uint32_t *)(S + L.g_cnt);
 	sa.g_base = (uint32_t *)(S + L.g_base); sa.g_dirty = (uint8_t *)(S + L.g_dirty);
 	sa.g_src = (uint32_t *)(S + L.g_src); sa.g_sel = (uint8_t *)(S + L.g_sel);
-	if (out) {
-		sa.frame_off = out->frame_off; sa.frame_len = out->frame_len; sa.session = out->session;
-		sa.cap_frames = out->cap_frames;
-		sa.sess_consumed = out->sess_consumed; sa.sess_bad = out->sess_bad_length_at;
-		sa.sess_first = out->sess_first_frame;
-	}
+	sa.g_sf = (uint32_t *)(S + L.g_sf); sa.g_openlocal = (uint32_t *)(S + L.g_openlocal);
+	sa.g_ssrc = (uint32_t *)(S + L.g_ssrc); sa.g_sub = (uint16_t *)(S + L.g_sub);
 	sa.ctrl = ctx->d_ctrl;
 	return ZKB_OK;
 }
@@ -1755,7 +1918,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	const ScratchLayout L = zk_layout(nbytes);
 	if ((rc = zk_ensure(ctx, &ctx->d_scratch, &ctx->d_scratch_bytes, L.total + 256, 0))) return rc;
 	SplitArgs sa;
-	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, NULL);
+	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess);
 	ScanVal *blk = (ScanVal *)((uint8_t *)ctx->d_scratch + L.blk);
 
 	const uint32_t split_blocks = (L.n_gran + 127) / 128;
@@ -1817,14 +1980,8 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	const ScratchLayout L = zk_layout(nbytes);
 	uint8_t *S = (uint8_t *)ctx->d_scratch;
 	SplitArgs sa;
-	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, out);
-	const uint32_t split_blocks = (L.n_gran + 127) / 128;
-	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->ticket, 0, sizeof (unsigned int), ctx->stream));
+	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess);
 	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long) * 9, ctx->stream));
-	ZK_EV(ctx, 2);
-	k_split<MODE_EMIT><<<split_blocks, 128, 0, ctx->stream>>>(sa);
-	LAUNCH_CHECK(ctx);
-	ZK_EV(ctx, 3);
 	/* sess_first_frame[nsess] = n_frames */
 	ZK_CUDA(ctx, cudaMemcpyAsync(out->sess_first_frame + nsess, &ctx->d_ctrl->n_frames, sizeof (uint32_t),
 	    cudaMemcpyDeviceToDevice, ctx->stream));
@@ -1836,7 +1993,10 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	if (xid && xid->ops) {
 		da.xt_base = xid->base; da.xt_count = xid->count; da.xt_off = xid->off; da.xt_ops = xid->ops;
 	}
-	da.g_base = sa.g_base; da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_chunks = L.n_chunks;
+	da.sess_off = sess->off; da.nsess = nsess;
+	da.g_base = sa.g_base; da.g_carry = sa.g_carry; da.g_sf = sa.g_sf; da.g_ssrc = sa.g_ssrc;
+	da.g_openlocal = sa.g_openlocal; da.g_sub = sa.g_sub; da.g_sel = sa.g_sel;
+	da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_chunks = L.n_chunks;
 	da.n_frames = n_frames; da.o = *out;
 	da.lb = (uint4 *)(S + L.lb); da.ctrl = ctx->d_ctrl;
 	ZK_CUDA(ctx, cudaMemsetAsync(da.lb, 0, (size_t)L.n_chunks * 16, ctx->stream));
@@ -1847,7 +2007,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	if ((rc = zk_read_ctrl(ctx))) return rc;
 	if (ctx->timing) {
 		cudaEventElapsedTime(&ctx->phase_ms[0], ctx->ev[0], ctx->ev[1]);
-		cudaEventElapsedTime(&ctx->phase_ms[1], ctx->ev[2], ctx->ev[3]);
+		ctx->phase_ms[1] = 0.0f;   /* the frame rows are written by the decode kernel itself */
 		cudaEventElapsedTime(&ctx->phase_ms[2], ctx->ev[4], ctx->ev[5]);
 	}
 	if (ctx->h_ctrl->error) {

@@ -13,7 +13,7 @@
 #include "../../include/zkbatch.h"
 
 /* ---- geometry ---------------------------------------------------------------------- */
-#define ZK_GRAN_MIN_LOG2     10   /* splitter granule: 1 KiB .. 8 KiB (= one decode chunk) */
+#define ZK_GRAN_MIN_LOG2     11   /* splitter granule: 2 KiB .. 8 KiB (= one decode chunk) */
 #define ZK_GRAN_MAX_LOG2     13
 #define ZK_MAX_BATCH_BYTES ((1ull << 34) - 1)  /* keeps every row index below 2^32 */
 
