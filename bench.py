@@ -63,6 +63,18 @@ def measured_peak():
     return 6650.0, "fallback"
 
 
+def pcie_roofline(h2d_gbps_per_gpu):
+    """e2e is bound by the upload: fraction of the measured duplex PCIe rate (profiles/pcie_peak.json)."""
+    p = os.path.join(ROOT, "profiles", "pcie_peak.json")
+    try:
+        with open(p) as f:
+            peak = float(json.load(f)["duplex_h2d_equiv_gbs"])
+        return {"bound": "pcie", "achieved": h2d_gbps_per_gpu, "peak": peak, "unit": "GB/s per GPU (upload)",
+                "frac": h2d_gbps_per_gpu / peak, "peak_source": "profiles/pcie_peak.json (measured on this pool)"}
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
@@ -405,7 +417,8 @@ def run_ours(args, rank, local_rank, world):
         "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                "wire_GBps": total_bytes / (e2e_ms / e2e_steps * 1e-3) / 1e9},
+                "wire_GBps": total_bytes / (e2e_ms / e2e_steps * 1e-3) / 1e9,
+                "pcie_roofline": pcie_roofline(total_bytes / (e2e_ms / e2e_steps * 1e-3) / 1e9 / max(world, 1))},
         "gpu_launches": int(launches),
         "split_fixups": ctx.split_fixups,
         "clocks": clocks,

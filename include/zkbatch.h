@@ -327,7 +327,7 @@ int zkb_decode_host(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbytes,
  * them, decode the server->client streams with that map.  Session i of `req` pairs with
  * session i of `rsp`; xids [xid_base[i], xid_base[i] + xid_count[i]) are tracked per session.
  *
- * The sessions are cut into slices of about `slice_bytes` (0 = default, 256 MiB) and the
+ * The sessions are cut into slices of about `slice_bytes` (0 = default, 512 MiB) and the
  * slices flow through three CUDA streams — upload, decode, download — so the PCIe transfers of
  * neighbouring slices overlap the kernels.  Results are handed to `cb` one slice at a time, in
  * session order, as context-owned pinned host columns that stay valid until `cb` returns:

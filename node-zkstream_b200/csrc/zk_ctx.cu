@@ -546,7 +546,7 @@ ZKB_EXPORT int zkb_replay_host(zkb_ctx *ctx,
 			ZK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_out[i], cudaEventDisableTiming));
 		}
 	}
-	if (slice_bytes == 0) slice_bytes = 256ull << 20;
+	if (slice_bytes == 0) slice_bytes = 512ull << 20;
 
 	/* ---- cut the sessions into slices ---- */
 	uint32_t nslices = 0, cap_slices = 16;

@@ -204,6 +204,9 @@ __device__ __forceinline__ int32_t win_be32(const uint4 &a, const uint4 &b, cons
 	return (int32_t)bswap32(__funnelshift_r(win_word<K / 4>(a, b, c), win_word<K / 4 + 1>(a, b, c), (K % 4) * 8));
 }
 
+#ifndef ZK_GUESS_HOPS
+#define ZK_GUESS_HOPS 3
+#endif
 struct GuessCtx {
 	const uint8_t *bytes;
 	uint64_t lim, send;
@@ -277,6 +280,11 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 			}
 			v0 = v1; v1 = v2;
 		}
+#ifdef ZK_PROFILE_PHASES
+		const long long gp_t0 = clock64();
+		atomicAdd(&a.ctrl->prof[4], 1ull);                                   /* segments scanned (per lane) */
+		atomicAdd(&a.ctrl->prof[5], (unsigned long long)(__popcll(cand_lo) + __popcll(cand_hi)));  /* candidates */
+#endif
 		/* phase 2: the far checks, candidate by candidate in stream order */
 #pragma unroll 1
 		for (int half = 0; half < 2; ++half) {
@@ -286,9 +294,17 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 				cand &= cand - 1;
 				const uint64_t p = seg + 64 * half + (uint64_t)k;
 				const int32_t len = (int32_t)g_be32(a.bytes, p);
-				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, 3)) return p;
+				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, ZK_GUESS_HOPS)) {
+#ifdef ZK_PROFILE_PHASES
+					atomicAdd(&a.ctrl->prof[3], (unsigned long long)(clock64() - gp_t0));
+#endif
+					return p;
+				}
 			}
 		}
+#ifdef ZK_PROFILE_PHASES
+		atomicAdd(&a.ctrl->prof[3], (unsigned long long)(clock64() - gp_t0));     /* cycles in phase 2 (per lane) */
+#endif
 	}
 	return ZK_NONE;
 }

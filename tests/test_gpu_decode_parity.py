@@ -134,3 +134,84 @@ def test_adversarial_split(ctx, oracle, synth):
     assert g.diff(o) == []
     assert g.n_frames == 3001
     print("split fixups used:", ctx.split_fixups - before)
+
+
+def test_native_cfg2_parity_at_size(ctx, oracle, synth, zk):
+    """~190 MB of the bench workload (C generator), both directions, every column vs the oracle."""
+    pc = synth.native_cfg2(5, 24, 20000)
+    n = pc.nsessions
+    req_g = ctx.decode_host(pc.req, pc.req_off, pc.req_flags, None, None)
+    req_o = oracle.decode(pc.req, pc.req_off, pc.req_flags, None, None)
+    assert req_g.diff(req_o) == []
+    layout = zk.XidTable(np.zeros(n, np.int32), np.full(n, pc.frames, np.uint32))
+    xt = ctx.xidtab_build_host(req_g, layout)
+    assert np.array_equal(xt.ops, pc.ops)
+    rsp_g = ctx.decode_host(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt)
+    rsp_o = oracle.decode(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt)
+    assert rsp_g.diff(rsp_o) == []
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_many_small_sessions_and_handshake_depths(ctx, oracle, synth, seed):
+    """Hundreds of sessions per 8 KiB chunk, empty ones included, with 0..3 (and 'always')
+    handshake frames: exercises session lookup, first-frame bookkeeping and per-session results
+    inside the decode kernel."""
+    import random
+    rng = random.Random(seed)
+    c = synth.Corpus()
+    for _ in range(1500):
+        server = rng.random() < 0.5
+        hs = rng.choice([0, 1, 1, 2, 3, 0xFFFFFFFF])
+        nf = rng.choice([0, 0, 1, 1, 2, 3, 5])
+        parts = []
+        xm = {}
+        for i in range(nf):
+            if server:
+                pl = synth.connect_request(rng) if rng.random() < 0.3 else (
+                    synth.be32(i) + synth.be32(4) + synth.request_body(rng, 4))
+            else:
+                if rng.random() < 0.3:
+                    pl = synth.connect_response(rng)
+                else:
+                    pl = synth.resp_header(i, i, 0) + synth.response_body(rng, 3)
+                    xm[i] = 3
+            parts.append(synth.frame(pl))
+        tail = rng.choice([b"", b"", b"\x00", b"\x00\x00\x00\x10\x00", b"\xff\xff\xff\xff"])
+        c.add(b"".join(parts) + tail, server=server, hs=hs, xidmap=xm)
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+
+
+def test_sessions_aligned_to_chunk_and_subrange_edges(ctx, oracle, synth):
+    """Session and frame boundaries exactly on 256-byte, 8 KiB and batch edges."""
+    import random
+    rng = random.Random(3)
+    c = synth.Corpus()
+
+    def filler(nbytes, i0=0):
+        """frames that add up to exactly nbytes (GET_DATA replies with sized payloads)"""
+        out, xm, i = [], {}, i0
+        left = nbytes
+        while left > 0:
+            if left < 200:
+                size = left
+            else:
+                size = rng.choice([96, 128, 256, 100, 180])
+                if left - size < 96:
+                    size = left
+            body = size - 4 - 16 - 4 - 68
+            assert body >= 0
+            out.append(synth.frame(synth.resp_header(i, i, 0) + synth.jbuf(bytes(body)) + synth.stat_bytes(rng)))
+            xm[i] = 4
+            i += 1
+            left -= size
+        return b"".join(out), xm
+
+    for nbytes in (8192, 256, 8192 - 256, 16384, 512, 8192 + 256):
+        data, xm = filler(nbytes)
+        assert len(data) == nbytes
+        c.add(data, hs=0, xidmap=xm)
+        c.add(b"", hs=1)
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+    assert (g.status == 0).all()

@@ -36,6 +36,9 @@ for label, data, off, fl, xt in (("request streams", pc.req, pc.req_off, pc.req_
     if sp[2]:
         print(label, "k_split<SPEC> per warp: guess %.0f cycles, walk %.0f cycles (%d warps)" % (
             sp[0] / sp[2], sp[1] / sp[2], sp[2]))
+        lanes = sp[2] * 32
+        print("     per lane: %.2f segments of 128 B scanned, %.2f candidates, %.0f cycles in far validation" % (
+            sp[4] / lanes, sp[5] / lanes, sp[3] / lanes))
     out = (C.c_ulonglong * 8)()
     lib.zkb_debug_phase_cycles(ctx._h, C.byref(out))
     n = max(1, out[7])
