@@ -110,6 +110,10 @@ extern "C" __attribute__((visibility("default"))) void zkb_debug_split_cycles(co
 {
 	memcpy(out, ctx->split_prof, sizeof (ctx->split_prof));
 }
+extern "C" __attribute__((visibility("default"))) void zkb_debug_split_iters(const zkb_ctx *ctx, unsigned int out[64])
+{
+	memcpy(out, ctx->split_iters, sizeof (ctx->split_iters));
+}
 #endif
 ZKB_EXPORT int zkb_ctx_set_timing(zkb_ctx *ctx, int on)
 {

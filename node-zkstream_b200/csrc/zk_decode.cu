@@ -334,6 +334,51 @@ __device__ uint64_t walk_chain(const SplitArgs &a, uint64_t pos, uint64_t send, 
 	}
 }
 
+/* One granule's walk: the chain that enters at `assumed` (if that lies inside the granule)
+ * and then every session that starts inside it.  Fills the granule's row of sub-range
+ * entries; `out` is where the last chain stands afterwards (ZK_INHERIT if nothing was walked). */
+struct GranWalk { uint64_t out; uint32_t count; uint32_t open_local; };
+
+__device__ GranWalk walk_granule(const SplitArgs &a, uint32_t g, uint32_t sf, uint64_t assumed, uint16_t *row)
+{
+	const uint64_t gs = (uint64_t)g << a.glog2;
+	const bool last = (g == a.n_gran - 1);
+	const uint64_t ge = last ? a.nbytes : gs + (1ull << a.glog2);
+	const uint32_t subs = 1u << (a.glog2 - 8);
+	for (uint32_t i = 0; i < subs; i += 8)
+		*reinterpret_cast<uint4 *>(row + i) = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+	GranWalk w; w.count = 0; w.open_local = 0;
+	uint64_t pos = ZK_NONE;
+	bool touched = false;
+	uint32_t last_sub = 0xFFFFFFFFu;
+	if (__ldg(a.sess_off + sf) != gs && assumed >= gs && assumed < ge) {   /* inside session sf-1 */
+		touched = true;
+		pos = walk_chain(a, assumed, __ldg(a.sess_off + sf), ge, w.count, gs, row, last_sub);
+	}
+	for (uint32_t s = sf; s < a.nsess; ++s) {
+		uint64_t so = __ldg(a.sess_off + s);
+		if (!(so < ge || last)) break;
+		touched = true;
+		w.open_local = w.count;
+		pos = walk_chain(a, so, __ldg(a.sess_off + s + 1), ge, w.count, gs, row, last_sub);
+	}
+	w.out = touched ? pos : ZK_INHERIT;
+	return w;
+}
+
+/* A dirty granule's carried position can be trusted when the granule that produced it is
+ * itself consistent and it does not point into an earlier granule. */
+__device__ __forceinline__ bool fix_trusted(const SplitArgs &a, uint32_t g)
+{
+	const uint32_t src = a.g_src[g];
+	const uint64_t carry = a.g_carry[g];
+	return !(src && a.g_dirty[src - 1]) && !(carry != ZK_NONE && carry < ((uint64_t)g << a.glog2));
+}
+
+#ifndef ZK_FIX_EXT
+#define ZK_FIX_EXT 64   /* granules one fix-up thread may carry its corrected chain through */
+#endif
+
 template <int MODE>
 __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 {
@@ -343,55 +388,27 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 	const uint64_t gs = (uint64_t)g << a.glog2;
 	const bool last = (g == a.n_gran - 1);
 	const uint64_t ge = last ? a.nbytes : gs + (1ull << a.glog2);
-
-#ifdef ZK_PROFILE_PHASES
-	const long long sp_t0 = clock64();
-#endif
-	uint32_t sf = (MODE == MODE_SPEC) ? lower_bound_u64(a.sess_off, a.nsess + 1, gs) : a.g_sf[g];
-	if (sf > a.nsess) return;   /* offsets do not cover the batch: k_check_sessions reports it */
-	bool cont = (__ldg(a.sess_off + sf) != gs);   /* granule starts inside session sf-1 */
-	uint64_t assumed = ZK_NONE, pos = ZK_NONE;
-	uint32_t count = 0, open_local = 0;
-	bool touched = false, has_start = false;
-
-	if (cont) {
-		uint32_t s = sf - 1;
-		uint64_t send = __ldg(a.sess_off + sf);
-		assumed = (MODE == MODE_SPEC) ? guess_entry(a, s, gs, ge, send) : a.g_carry[g];
-	}
-	if (MODE == MODE_SPEC) __syncwarp();   /* lanes finish guessing at different times: walk together */
-#ifdef ZK_PROFILE_PHASES
-	const long long sp_t1 = clock64();
-#endif
-	/* this walk's row of sub-range entries: version 0 (and 1, copied below) in SPEC, version 1 in FIX */
 	const uint32_t subs = 1u << (a.glog2 - 8);
-	uint16_t *row = a.g_sub + ((size_t)(MODE == MODE_SPEC ? 0 : a.n_gran) + g) * subs;
-	for (uint32_t i = 0; i < subs; i += 8)
-		*reinterpret_cast<uint4 *>(row + i) = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-	uint32_t last_sub = 0xFFFFFFFFu;
-	if (cont) {
-		uint64_t send = __ldg(a.sess_off + sf);
-		if (assumed >= gs && assumed < ge) {
-			touched = true;
-			pos = walk_chain(a, assumed, send, ge, count, gs, row, last_sub);
-		}
-	}
-	for (uint32_t s = sf; s < a.nsess; ++s) {
-		uint64_t so = __ldg(a.sess_off + s);
-		if (!(so < ge || last)) break;
-		touched = true;
-		has_start = true;
-		open_local = count;
-		pos = walk_chain(a, so, __ldg(a.sess_off + s + 1), ge, count, gs, row, last_sub);
-	}
+
 	if (MODE == MODE_SPEC) {
+#ifdef ZK_PROFILE_PHASES
+		const long long sp_t0 = clock64();
+#endif
+		const uint32_t sf = lower_bound_u64(a.sess_off, a.nsess + 1, gs);
+		if (sf > a.nsess) return;   /* offsets do not cover the batch: k_check_sessions reports it */
+		uint64_t assumed = ZK_NONE;
+		if (__ldg(a.sess_off + sf) != gs)   /* granule starts inside session sf-1 */
+			assumed = guess_entry(a, sf - 1, gs, ge, __ldg(a.sess_off + sf));
+		__syncwarp();   /* lanes finish guessing at different times: walk together */
+#ifdef ZK_PROFILE_PHASES
+		const long long sp_t1 = clock64();
+#endif
+		uint16_t *row = a.g_sub + (size_t)g * subs;
+		const GranWalk w = walk_granule(a, g, sf, assumed, row);
 		uint16_t *row1 = a.g_sub + ((size_t)a.n_gran + g) * subs;
 		for (uint32_t i = 0; i < subs; i += 8)
 			*reinterpret_cast<uint4 *>(row1 + i) = *reinterpret_cast<const uint4 *>(row + i);
-	}
-	const uint64_t out = touched ? pos : ZK_INHERIT;
 #ifdef ZK_PROFILE_PHASES
-	if (MODE == MODE_SPEC) {
 		__syncwarp();
 		const long long sp_t2 = clock64();
 		if ((threadIdx.x & 31) == 0) {
@@ -399,28 +416,64 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 			atomicAdd(&a.ctrl->prof[1], (unsigned long long)(sp_t2 - sp_t1));
 			atomicAdd(&a.ctrl->prof[2], 1ull);
 		}
-	}
 #endif
-	if (MODE == MODE_SPEC) {
-		a.g_assumed[g] = assumed; a.g_out[g] = out; a.g_cnt[g] = count; a.g_openlocal[g] = open_local;
-		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = out; a.g_cnt[a.n_gran + g] = count;
-		a.g_openlocal[a.n_gran + g] = open_local;
+		a.g_assumed[g] = assumed; a.g_out[g] = w.out; a.g_cnt[g] = w.count; a.g_openlocal[g] = w.open_local;
+		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = w.out; a.g_cnt[a.n_gran + g] = w.count;
+		a.g_openlocal[a.n_gran + g] = w.open_local;
 		a.g_sel[g] = 0;
 		a.g_sf[g] = sf;
-		(void)has_start;
-	} else {
-		/* Every dirty granule re-walks from its carried position, but the result only
-		 * replaces the guess-based one in the next scan if that position can be trusted:
-		 * the granule that produced it is itself consistent, and it does not land in an
-		 * earlier granule.  Otherwise the scan keeps using the walk from the granule's own
-		 * guess, whose exit is usually right even when its entry was not, so one bad guess
-		 * cannot push an error wave down the stream.  The lowest dirty granule always
-		 * qualifies, so every iteration makes progress. */
-		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = out; a.g_cnt[a.n_gran + g] = count;
-		a.g_openlocal[a.n_gran + g] = open_local;
-		const uint32_t src = a.g_src[g];
-		const bool trusted = !(src && a.g_dirty[src - 1]) && !(assumed != ZK_NONE && assumed < gs);
-		a.g_sel[g] = trusted ? 1 : 0;
+		return;
+	}
+
+	/* FIX.  Only a dirty granule whose carried position can be trusted acts (the lowest dirty
+	 * granule always qualifies, so every iteration makes progress); the others keep the walk
+	 * from their own guess, whose exit is usually right even when its entry was not, so one
+	 * bad guess cannot push an error wave down the stream.  The acting thread re-walks its
+	 * granule into version 1 and then carries the corrected chain through the granules that
+	 * follow - switching them to whichever recorded walk agrees with it, or re-walking them -
+	 * until it reaches a granule that already agrees (the chains have merged) or another
+	 * trusted dirty granule (which has its own thread).  The runs of two acting threads are
+	 * disjoint, so nothing here is written twice.  The scan that follows re-verifies every
+	 * granule, so a run cut short by ZK_FIX_EXT only costs another iteration. */
+	if (!fix_trusted(a, g)) return;
+	uint64_t carry = a.g_carry[g];
+	{
+		const GranWalk w = walk_granule(a, g, a.g_sf[g], carry, a.g_sub + ((size_t)a.n_gran + g) * subs);
+		a.g_assumed[a.n_gran + g] = carry; a.g_out[a.n_gran + g] = w.out; a.g_cnt[a.n_gran + g] = w.count;
+		a.g_openlocal[a.n_gran + g] = w.open_local;
+		a.g_sel[g] = 1;
+		if (w.out != ZK_INHERIT) carry = w.out;
+	}
+	for (uint32_t h = g + 1, steps = 0; h < a.n_gran && steps < ZK_FIX_EXT; ++h, ++steps) {
+		if (a.g_dirty[h] && fix_trusted(a, h)) break;
+		const uint64_t hs = (uint64_t)h << a.glog2;
+		const uint64_t he = (h == a.n_gran - 1) ? a.nbytes : hs + (1ull << a.glog2);
+		const uint64_t nc = (carry >= hs && carry < he) ? carry : ZK_NONE;
+		uint8_t sel = a.g_sel[h];
+		const uint64_t as = a.g_assumed[(size_t)sel * a.n_gran + h];
+		const uint64_t ao = a.g_assumed[(size_t)(sel ^ 1) * a.n_gran + h];
+		bool changed = false;
+		uint64_t hout;
+		if (((as >= hs && as < he) ? as : ZK_NONE) == nc) {
+			hout = a.g_out[(size_t)sel * a.n_gran + h];
+		} else if (((ao >= hs && ao < he) ? ao : ZK_NONE) == nc) {
+			sel ^= 1;
+			a.g_sel[h] = sel;
+			hout = a.g_out[(size_t)sel * a.n_gran + h];
+			changed = true;
+		} else {
+			const GranWalk w = walk_granule(a, h, a.g_sf[h], nc, a.g_sub + ((size_t)a.n_gran + h) * subs);
+			a.g_assumed[a.n_gran + h] = nc; a.g_out[a.n_gran + h] = w.out; a.g_cnt[a.n_gran + h] = w.count;
+			a.g_openlocal[a.n_gran + h] = w.open_local;
+			a.g_sel[h] = 1;
+			hout = w.out;
+			changed = true;
+		}
+		if (hout == ZK_INHERIT) continue;          /* nothing starts in h: the carry passes through */
+		carry = hout;
+		if (changed) continue;                       /* what h hands on may differ from what was scanned */
+		if (h + 1 < a.n_gran && a.g_dirty[h + 1] && !fix_trusted(a, h + 1)) continue;
+		break;                                       /* merged with the chain the scan already has */
 	}
 }
 
@@ -1954,6 +2007,11 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 			snprintf(ctx->err, sizeof (ctx->err), "zkb_decode: session offsets invalid");
 			return ZKB_EINVAL;
 		}
+		if (iter < 32) {
+			ctx->split_iters[iter][0] = ctx->h_ctrl->n_dirty;
+			ctx->split_iters[iter][1] = ctx->h_ctrl->n_rewalk;
+			if (iter < 31) ctx->split_iters[iter + 1][0] = ctx->split_iters[iter + 1][1] = 0;
+		}
 		if (ctx->h_ctrl->n_dirty == 0) break;
 		if (iter > L.n_gran + 2) {
 			snprintf(ctx->err, sizeof (ctx->err), "zkb_decode: splitter did not converge");
@@ -1961,7 +2019,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		}
 		ctx->split_fixups++;
 		const bool rewalk = ctx->h_ctrl->n_rewalk != 0;
-		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_dirty, 0, 2 * sizeof (unsigned int), ctx->stream));
+		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_dirty, 0, 3 * sizeof (unsigned int), ctx->stream));
 		if (rewalk) {
 			k_split<MODE_FIX><<<split_blocks, 128, 0, ctx->stream>>>(sa);
 			LAUNCH_CHECK(ctx);

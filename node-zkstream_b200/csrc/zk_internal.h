@@ -51,6 +51,7 @@ struct zkb_ctx {
 	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
 	unsigned long long prof[8];
 	unsigned long long split_prof[8];
+	unsigned int split_iters[32][2];  /* last split: (n_dirty, n_rewalk) after each scan */
 	/* device scratch (grown on demand, never shrunk) */
 	void         *d_scratch;   size_t d_scratch_bytes;
 	zk_ctrl      *d_ctrl;

@@ -39,6 +39,10 @@ for label, data, off, fl, xt in (("request streams", pc.req, pc.req_off, pc.req_
         lanes = sp[2] * 32
         print("     per lane: %.2f segments of 128 B scanned, %.2f candidates, %.0f cycles in far validation" % (
             sp[4] / lanes, sp[5] / lanes, sp[3] / lanes))
+    it = (C.c_uint * 64)()
+    lib.zkb_debug_split_iters.argtypes = [C.c_void_p, C.POINTER(C.c_uint * 64)]
+    lib.zkb_debug_split_iters(ctx._h, C.byref(it))
+    print(label, "split iterations (n_dirty, n_rewalk):", [(it[2 * i], it[2 * i + 1]) for i in range(32) if it[2 * i] or i == 0])
     out = (C.c_ulonglong * 8)()
     lib.zkb_debug_phase_cycles(ctx._h, C.byref(out))
     n = max(1, out[7])
