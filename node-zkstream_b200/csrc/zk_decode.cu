@@ -97,6 +97,12 @@ __device__ __forceinline__ uint4 ld_desc(const uint4 *p)
 	    : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
 	return r;
 }
+__device__ __forceinline__ uint32_t ld_state(const uint4 *p)
+{
+	uint32_t r;
+	asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+	return r;
+}
 __device__ __forceinline__ void st_desc(uint4 *p, uint4 v)
 {
 	asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};"
@@ -1374,6 +1380,9 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane)
  * in each phase (ticket, staging wait, frame loop, counts, look-back, emission) into
  * zk_ctrl::prof; read them with zkb_debug_phase_cycles().  Off in normal builds. */
 #ifdef ZK_PROFILE_PHASES
+/* histogram of cycles from tile issue to AGG publish (1024-cycle buckets), chunks without /
+ * with generic-parser frames; and of the look-back wait */
+__device__ unsigned long long zk_hist[3][64];
 #define ZK_T(i) const long long zk_t##i = clock64()
 #define ZK_ACC(slot, a, b) do { if (lane == 0) atomicAdd(&a_ctrl_prof[slot], (unsigned long long)((b) - (a))); } while (0)
 #else
@@ -1677,6 +1686,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 				if (idx >= 0) d[q] = ld_desc(a.lb + idx);
 			}
 			bool done = false, wait = false;
+			int64_t hole_idx = 0;
 			uint32_t s0 = 0, s1 = 0, s2 = 0;
 #pragma unroll
 			for (int q = 0; q < 4; ++q) {
@@ -1685,18 +1695,26 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 				const uint32_t em = __ballot_sync(0xffffffffu, d[q].x == ZK_LB_EMPTY);
 				const int first = __ffs(pm) - 1;       /* nearest full prefix in this group */
 				const int hole = __ffs(em) - 1;        /* nearest chunk that has published nothing */
-				if (hole >= 0 && (first < 0 || hole < first)) { wait = true; continue; }
+				if (hole >= 0 && (first < 0 || hole < first)) { wait = true; hole_idx = j - 32 * q - hole; continue; }
 				const bool use = (first < 0 || (int)lane <= first);
 				s0 += use ? d[q].y : 0u; s1 += use ? d[q].z : 0u; s2 += use ? d[q].w : 0u;
 				if (first >= 0) done = true;
 			}
 			if (wait) {
-				if (++spins > ZK_SPIN_LIMIT) {
+				/* Wait on that one chunk (a single word, the same address for the whole warp)
+				 * instead of re-reading the window: a spinning warp takes issue slots from the
+				 * warps still parsing, so the poll is kept to a handful of instructions. */
+				bool gave_up = false;
+				for (;;) {
+					if (++spins > ZK_SPIN_LIMIT) { gave_up = true; break; }
+					__nanosleep(ns_sleep);
+					if (ns_sleep < 1024) ns_sleep <<= 1;
+					if (ld_state(a.lb + hole_idx) != ZK_LB_EMPTY) break;
+				}
+				if (gave_up) {
 					if (lane == 0) atomicOr(&a.ctrl->error, ZK_DERR_LOOKBACK);
 					break;
 				}
-				__nanosleep(ns_sleep);
-				if (ns_sleep < 1024) ns_sleep <<= 1;
 				continue;
 			}
 			e0 += warp_sum(s0); e1 += warp_sum(s1); e2 += warp_sum(s2);
@@ -1715,6 +1733,14 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	ZK_T(6);
 	ZK_ACC(0, zk_t0, zk_t1); ZK_ACC(1, zk_t1, zk_t2); ZK_ACC(2, zk_t2, zk_t3); ZK_ACC(3, zk_t3, zk_t4);
 	ZK_ACC(4, zk_t4, zk_t5); ZK_ACC(5, zk_t5, zk_t6);
+#ifdef ZK_PROFILE_PHASES
+	if (lane == 0) {
+		unsigned long long b = (unsigned long long)(zk_t5 - zk_t1) >> 11; if (b > 63) b = 63;
+		atomicAdd(&zk_hist[n_slow ? 1 : 0][b], 1ull);
+		b = (unsigned long long)(zk_t6 - zk_t5) >> 11; if (b > 63) b = 63;
+		atomicAdd(&zk_hist[2][b], 1ull);
+	}
+#endif
 	if (ts + tb + ta == 0) return;
 
 	/* ---- emit: compact each bitmap, lane w owns bitmap word w (128 input bytes) ---- */
@@ -2029,6 +2055,14 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	memcpy(ctx->split_prof, ctx->h_ctrl->prof, sizeof (ctx->split_prof));
 	return ZKB_OK;
 }
+
+#ifdef ZK_PROFILE_PHASES
+extern "C" __attribute__((visibility("default"))) void zkb_debug_hist(unsigned long long out[192], int reset)
+{
+	cudaMemcpyFromSymbol(out, zk_hist, sizeof (zk_hist));
+	if (reset) { static unsigned long long z[192]; cudaMemcpyToSymbol(zk_hist, z, sizeof (z)); }
+}
+#endif
 
 /* Phase B: write the frame rows and decode every frame.  Must follow zk_split_device on
  * the same batch (it reuses the granule tables in the context's scratch). */

@@ -28,8 +28,25 @@ for label, data, off, fl, xt in (("request streams", pc.req, pc.req_off, pc.req_
     ds = dev.DeviceSessions(data.size, off, fl, None, device)
     dx = dev.DeviceXidTable(xt, device) if xt is not None else None
     dc = dev.decode_dev_autosize(ctx, d, int(data.size), ds, dx, device=device)
-    for _ in range(3):
+    hist = (C.c_ulonglong * 192)()
+    for it in range(3):
+        if it == 2:
+            lib.zkb_debug_hist(C.byref(hist), 1)
         dev.decode_dev(ctx, d, int(data.size), ds, dx, dc)
+    import torch
+    torch.cuda.synchronize()
+    lib.zkb_debug_hist(C.byref(hist), 0)
+    for hi, nm in enumerate(("issue->AGG, fast chunks", "issue->AGG, chunks with generic-parser frames", "look-back wait")):
+        h = [hist[hi * 64 + b] for b in range(64)]
+        tot = max(1, sum(h))
+        cum, qs = 0, {}
+        for b, v in enumerate(h):
+            cum += v
+            for q in (0.5, 0.9, 0.99, 0.999, 1.0):
+                if q not in qs and cum >= q * tot:
+                    qs[q] = (b + 1) * 2048
+        print("   hist %-46s n=%8d  p50 %6d p90 %6d p99 %6d p99.9 %6d max %6d cycles" % (
+            nm, sum(h), qs[0.5], qs[0.9], qs[0.99], qs[0.999], qs[1.0]))
     sp = (C.c_ulonglong * 8)()
     lib.zkb_debug_split_cycles.argtypes = [C.c_void_p, C.POINTER(C.c_ulonglong * 8)]
     lib.zkb_debug_split_cycles(ctx._h, C.byref(sp))
