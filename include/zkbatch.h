@@ -390,6 +390,50 @@ int zkb_xidtab_build_dev(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsession
 int zkb_xidtab_build_noalloc(const zkb_decoded *req, uint32_t nsessions, const zkb_xidtab *layout,
     int8_t *ops_out, void *stream, char *errbuf, size_t errcap);
 
+/* ---- session-level reductions --------------------------------------------------------- */
+
+/*
+ * What ZKSession folds out of the decoded server->client packets one at a time while a
+ * connection is attached (lib/zk-session.js:227-236 and processNotification, :389-419),
+ * as per-session reductions over a decoded RESPONSE stream:
+ *
+ *  max_zxid[s], n_replies[s]   every OK frame of kind RESPONSE whose opcode is not NOTIFICATION
+ *      takes the zxid branch (:229-235): n_replies counts them, max_zxid is the greatest zxid
+ *      among them under BigInteger.compareTo, i.e. as signed 64-bit integers (INT64_MIN when
+ *      there were none).  The session's zs_lastZxid, which starts at 0 (:57), becomes
+ *      max(zs_lastZxid, max_zxid[s]) — the binding does that fold, so a session carried across
+ *      batches keeps its value.  jsbn is not vendored with the reference, so the signedness of
+ *      this compare rests on jsbn's documented byte-array constructor, not on a reference test.
+ *  notifications[s * ZKB_NOTIFY_SLOTS + k]   NOTIFICATION frames by what processNotification
+ *      does with them: k = ZKB_NOTIFY_IGNORED when pkt.state is not 'SYNC_CONNECTED' (logged and
+ *      dropped, :391-400 — that includes error replies, whose body is never read); k = 1..4 the
+ *      event counted at :413-415, by NOTIFICATION_TYPE value (CREATED, DELETED, DATA_CHANGED,
+ *      CHILDREN_CHANGED, zk-consts.js:111-116); k = ZKB_NOTIFY_BAD_TYPE when the type is outside
+ *      that table (pkt.type is undefined and :402 throws a TypeError).
+ *
+ * Frames that are not OK (BAD_DECODE) never became packets and are skipped.  With
+ * ZKB_STATS_UNTIL_ERROR only the frames before a session's first BAD_DECODE frame count: the
+ * reference tears the connection down on the decoder's first 'error' (connection-fsm.js:234-239),
+ * so nothing later would have reached the session.
+ */
+#define ZKB_NOTIFY_SLOTS     6
+#define ZKB_NOTIFY_IGNORED   0
+#define ZKB_NOTIFY_BAD_TYPE  5
+#define ZKB_STATS_UNTIL_ERROR 1u
+
+typedef struct zkb_session_stats {
+	int64_t  *max_zxid;       /* [nsessions] */
+	uint32_t *n_replies;      /* [nsessions] */
+	uint32_t *notifications;  /* [nsessions * ZKB_NOTIFY_SLOTS] */
+} zkb_session_stats;
+
+/* Device pointers in `dec` (meta, session, zxid, a0, a1 and n_frames are read) and in `out`. */
+int zkb_session_stats_dev(zkb_ctx *ctx, const zkb_decoded *dec, uint32_t nsessions, uint32_t flags,
+    zkb_session_stats *out);
+/* Host pointers in `dec` and `out`. */
+int zkb_session_stats_host(zkb_ctx *ctx, const zkb_decoded *dec, uint32_t nsessions, uint32_t flags,
+    zkb_session_stats *out);
+
 /* ---- encode ----------------------------------------------------------------------------- */
 
 /*

@@ -14,7 +14,9 @@ from .materialise import LongDate, Materialiser
 from .encode import RequestBatch
 from .streams import ZKDecodeStream, ZKEncodeStream
 from .zkbuffer import JuteBuffer, ZKBuffer
+from .session import SessionStats, SessionState
 
 __all__ = ["Context", "XidTable", "ZKBatchError", "Columns", "load", "LIB_PATH", "consts",
            "ZKProtocolError", "ZKError", "LongDate", "Materialiser", "RequestBatch",
-           "ZKDecodeStream", "ZKEncodeStream", "JuteBuffer", "ZKBuffer"]
+           "ZKDecodeStream", "ZKEncodeStream", "JuteBuffer", "ZKBuffer",
+           "SessionStats", "SessionState"]

@@ -12,6 +12,8 @@ NO_OFFSET = 0xFFFFFFFFFFFFFFFF
 ENC_CONNECT_REQUEST, ENC_CONNECT_RESPONSE = -100, -101
 ENC_OK, ENC_UNSUPPORTED = 0, 1
 NOALLOC_MAX_XIDS = 1 << 20
+NOTIFY_SLOTS, NOTIFY_IGNORED, NOTIFY_BAD_TYPE = 6, 0, 5
+STATS_UNTIL_ERROR = 1
 
 FIELD_NAMES = [
     "NONE", "XID", "ZXID", "ERR", "OPCODE", "PATH", "DATA", "WATCH", "VERSION", "FLAGS",
@@ -65,6 +67,10 @@ class Requests(C.Structure):
                 ("acl_id_off", P), ("acl_id_len", P)]
 
 
+class SessionStats(C.Structure):
+    _fields_ = [("max_zxid", P), ("n_replies", P), ("notifications", P)]
+
+
 SLICE_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(Decoded), C.POINTER(Decoded))
 
 # every symbol include/zkbatch.h declares: (name, restype, argtypes)
@@ -88,6 +94,8 @@ SYMBOLS = [
     ("zkb_xidtab_build_dev", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P]),
     ("zkb_xidtab_build_noalloc", C.c_int, [C.POINTER(Decoded), C.c_uint32, C.POINTER(XidTab), P, P,
                                            C.c_char_p, C.c_size_t]),
+    ("zkb_session_stats_dev", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.c_uint32, C.POINTER(SessionStats)]),
+    ("zkb_session_stats_host", C.c_int, [P, C.POINTER(Decoded), C.c_uint32, C.c_uint32, C.POINTER(SessionStats)]),
     ("zkb_encode_dev", C.c_int, [P, C.POINTER(Requests), P, C.c_uint64, P, P, C.POINTER(C.c_uint64)]),
     ("zkb_encode_host", C.c_int, [P, C.POINTER(Requests), C.POINTER(P), C.POINTER(P), C.POINTER(P),
                                    C.POINTER(C.c_uint64)]),

@@ -226,6 +226,21 @@ class Context:
         self._check(self._lib.zkb_xidtab_build_host(self._h, C.byref(d), len(layout.count), C.byref(t), _ptr(ops)))
         return XidTable(layout.base, layout.count, ops)
 
+    # ---- session-level reductions ------------------------------------------------
+    def session_stats_host(self, cols, nsessions=None, flags=0):
+        """ZKSession's per-packet folds (max zxid, notification counts) over decoded response
+        columns `cols` -> session.SessionStats."""
+        from .session import SessionStats
+        n = cols.nsessions if nsessions is None else nsessions
+        d = _abi.Decoded()
+        d.n_frames = cols.n_frames
+        for name in ("meta", "session", "zxid", "a0", "a1"):
+            setattr(d, name, _ptr(getattr(cols, name)))
+        st = SessionStats.empty(n)
+        cs = st.struct()
+        self._check(self._lib.zkb_session_stats_host(self._h, C.byref(d), n, flags, C.byref(cs)))
+        return st
+
     # ---- encode -----------------------------------------------------------------
     def encode_host(self, req):
         """req: encode.RequestBatch.  Returns (bytes ndarray, frame_off ndarray, status ndarray)."""

@@ -134,3 +134,16 @@ def xidtab_build_dev(ctx, dcols_req, nsess, dxid):
     rc = ctx._lib.zkb_xidtab_build_dev(ctx._h, C.byref(dcols_req.struct), nsess, C.byref(dxid.struct),
                                        dxid.ops.data_ptr())
     ctx._check(rc)
+
+
+def session_stats_dev(ctx, dcols, nsess, flags=0, device="cuda:0"):
+    """zkb_session_stats_dev over device-resident columns -> session.SessionStats (host copy)."""
+    from .session import SessionStats
+    mx = torch.empty(max(nsess, 1), dtype=torch.int64, device=device)
+    nr = torch.empty(max(nsess, 1), dtype=torch.int32, device=device)
+    nt = torch.empty(max(nsess, 1) * _abi.NOTIFY_SLOTS, dtype=torch.int32, device=device)
+    st = _abi.SessionStats()
+    st.max_zxid, st.n_replies, st.notifications = mx.data_ptr(), nr.data_ptr(), nt.data_ptr()
+    ctx._check(ctx._lib.zkb_session_stats_dev(ctx._h, C.byref(dcols.struct), nsess, flags, C.byref(st)))
+    return SessionStats(mx[:nsess].cpu().numpy().copy(), nr[:nsess].cpu().numpy().view(np.uint32).copy(),
+                        nt[:nsess * _abi.NOTIFY_SLOTS].cpu().numpy().view(np.uint32).reshape(nsess, _abi.NOTIFY_SLOTS).copy())

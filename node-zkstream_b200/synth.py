@@ -337,6 +337,44 @@ def fuzz_corpus(seed, nsessions=24, max_frames=40, p_mutate=0.3, p_tail=0.3, p_b
     return c
 
 
+def session_corpus(seed, nsessions=12, max_frames=60):
+    """Client-side (server->client) sessions for the session-level folds: replies whose zxids
+    cover the signed range, notifications of every type and state (valid or not), error
+    notifications, frames that fail to decode, the odd damaged tail."""
+    rng = random.Random(0x5E55 + seed)
+    c = Corpus()
+    zx_pool = [0, 1, -1, 5, (1 << 63) - 1, -(1 << 63), 0x100000000, 0xFFFFFFFF, -0x100000000, 0x7FFFFFFF00000000]
+    for _ in range(nsessions):
+        parts, xm = [frame(connect_response(rng))], {}
+        hs = 1
+        if rng.random() < 0.15:
+            parts, hs = [], 0
+        nf = rng.randrange(0, max_frames)
+        for i in range(nf):
+            r = rng.random()
+            if r < 0.35:
+                t = rng.choice([1, 2, 3, 4, 4, 3, 0, 5, -1, 77])
+                st = rng.choice([3, 3, 3, 3, 0, 4, 5, 6, -122, 9])
+                err = rng.choice([0, 0, 0, 0, 0, -101, -4])
+                body = (be32(t) + be32(st) + jbuf(rpath(rng, 1, 12))) if err == 0 else b""
+                parts.append(frame(resp_header(-1, rng.choice([-1, -1, 7]), err) + body))
+            elif r < 0.45:
+                parts.append(frame(resp_header(-2, rng.choice(zx_pool), 0)))           # ping reply
+            elif r < 0.52:
+                parts.append(frame(resp_header(1000 + i, rng.choice(zx_pool), 0)))     # xid nobody sent
+            elif r < 0.56:
+                parts.append(frame(resp_header(i, 3, 0)[:rng.randrange(0, 15)]))       # short header
+            else:
+                op = rng.choice([1, 2, 3, 4, 5, 8, 9, 12])
+                err = rng.choice([0, 0, 0, -101, -110, -103])
+                zx = rng.choice(zx_pool) if rng.random() < 0.5 else rng.getrandbits(64) - (1 << 63)
+                parts.append(frame(resp_header(i, zx, err) + (response_body(rng, op) if err == 0 else b"")))
+                xm[i] = op
+        tail = rng.choice([b"", b"", b"", b"\x00\x00", b"\xff\xff\xff\xff", b"\x00\x00\x00\x20abc"])
+        c.add(b"".join(parts) + tail, hs=hs, xidmap=xm)
+    return c
+
+
 # ---- benchmark-scale corpora from the C generator (csrc/zkgen.c) --------------------------
 
 _gen = None

@@ -7,7 +7,9 @@ ref_decode.json: sessions of wire bytes (every reader, every damaged-frame shape
 synth.fuzz_corpus, the reference's own captures and bad-length prefixes) with the packets /
 errors ZKDecodeStream produced for them.  ref_encode.json: packets with the frames
 ZKEncodeStream produced.  The tests compare the CPU oracle and the CUDA codec with these
-files, so the GPU box never needs the reference.
+ref_session_folds.json: client-side sessions with what ZKSession's own packet handler
+(lib/zk-session.js) made of them.  The tests compare the CPU oracle and the CUDA codec with
+these files, so the GPU box never needs the reference.
 """
 import base64
 import importlib
@@ -113,8 +115,32 @@ def main():
     with open(os.path.join(GOLD, "ref_encode.json"), "w") as f:
         json.dump(dict(generator="oracle/make_golden.py", reference="node-zkstream lib/zk-streams.js ZKEncodeStream "
                        "run under oracle/_ref/js", packets=enc), f, separators=(",", ":"))
-    print("wrote %d decode sessions, %d encode packets" % (len(dec), len(enc)))
+    folds = []
+    for name, c in session_corpora():
+        sessions = [dict(chunks=[c.chunks[i]], hs=c.hs[i], xidMap=xidmap_names(c.xidmaps[i]))
+                    for i in range(len(c.chunks)) if not c.flags[i]]
+        keep = [i for i in range(len(c.chunks)) if not c.flags[i]]
+        ref_all = ref_js.session_folds(sessions, until_error=False)
+        ref_stop = ref_js.session_folds(sessions, until_error=True)
+        for j, i in enumerate(keep):
+            folds.append(dict(corpus=name, hex=c.chunks[i].hex(), hs=c.hs[i],
+                              xidMap={str(k): v for k, v in c.xidmaps[i].items()},
+                              all=ref_all[j], until_error=ref_stop[j]))
+    with open(os.path.join(GOLD, "ref_session_folds.json"), "w") as f:
+        json.dump(dict(generator="oracle/make_golden.py", reference="node-zkstream lib/zk-session.js: the 'packet' "
+                       "handler of state_attached and processNotification, fed by lib/zk-streams.js ZKDecodeStream, "
+                       "run under oracle/_ref/js (jsbn replaced by a signed big-endian stand-in)", sessions=folds),
+                  f, separators=(",", ":"))
+    print("wrote %d decode sessions, %d encode packets, %d session folds" % (len(dec), len(enc), len(folds)))
     return 0
+
+
+def session_corpora():
+    out = [("session%d" % seed, synth.session_corpus(seed)) for seed in range(6)]
+    out.append(("cfg3", synth.cfg3_tiny(4, 60, seed=16)))
+    out.append(("cfg2", synth.cfg2_mixed(2, 40, seed=15)))
+    out.append(("fuzz", synth.fuzz_corpus(21, nsessions=24, max_frames=24)))
+    return out
 
 
 def _jsonable(v):

@@ -168,9 +168,39 @@ Transform.prototype.push = function (x) { this._pushed.push(x); this._events.pus
 Transform.prototype.emit = function (ev, arg) { this._events.push({ ev: ev, arg: arg }); };
 var mod_stream_shim = { Transform: Transform };
 
-/* jsbn: only `instanceof`-free duck typing is used on the hot path (toByteArray) */
-function BigInteger(bytes) { this._b = bytes; }
+/* jsbn stand-in (the real one is not vendored): construction from a byte array or Buffer
+ * (big-endian two's complement, as jsbn documents) or a small decimal literal, toByteArray
+ * for the write path, and the signed compareTo / equals ZKSession uses on zxids. */
+function BigInteger(x) {
+	if (typeof (x) === 'string') {
+		var v = parseInt(x, 10), b = [], i;
+		for (i = 7; i >= 0; --i) { b[i] = v & 0xff; v = Math.floor(v / 256); }
+		this._b = b;
+	} else {
+		this._b = x;
+	}
+}
 BigInteger.prototype.toByteArray = function () { var r = []; for (var i = 0; i < this._b.length; ++i) r.push(this._b[i]); return r; };
+BigInteger.prototype._parts = function () {
+	/* [signed high word, unsigned low word] of the value sign-extended to 8 bytes */
+	var n = this._b.length, neg = (n > 0 && (this._b[0] & 0x80) !== 0), hi = 0, lo = 0, i, byte;
+	for (i = 0; i < 8; ++i) {
+		byte = (i < 8 - n) ? (neg ? 0xff : 0) : (this._b[i - (8 - n)] & 0xff);
+		if (i < 4) hi = hi * 256 + byte; else lo = lo * 256 + byte;
+	}
+	if (hi >= 2147483648) hi -= 4294967296;
+	return [hi, lo];
+};
+BigInteger.prototype.compareTo = function (o) {
+	var a = this._parts(), b = o._parts();
+	if (a[0] !== b[0]) return (a[0] < b[0] ? -1 : 1);
+	if (a[1] !== b[1]) return (a[1] < b[1] ? -1 : 1);
+	return 0;
+};
+BigInteger.prototype.equals = function (o) { return this.compareTo(o) === 0; };
+BigInteger.ZERO = new BigInteger('0');
+function EventEmitterStub() {}
+function FSMStub() {}
 
 var DEFS = {};
 var CACHE = {};
@@ -179,7 +209,9 @@ function requireShim(name) {
 	if (name === 'util') return mod_util_shim;
 	if (name === 'stream') return mod_stream_shim;
 	if (name === 'jsbn') return { BigInteger: BigInteger };
-	if (name === 'events') return {};
+	if (name === 'events') return { EventEmitter: EventEmitterStub };
+	if (name === 'mooremachine') return { FSM: FSMStub };
+	if (name === 'bunyan' || name === 'verror' || name === 'vasync') return {};
 	var key = name.replace(/^\.\//, '');
 	if (CACHE[key]) return CACHE[key].exports;
 	if (!DEFS[key]) throw new Error('no module ' + name);
@@ -283,9 +315,9 @@ function encodeSession(sess) {
 """
 
 
-def bundle():
+def bundle(files=None):
     parts = [SHIM_JS]
-    for name in REF_FILES:
+    for name in (files or REF_FILES):
         with open(os.path.join(REF, "lib", name + ".js")) as f:
             src = f.read()
         parts.append("DEFS[%s] = function (module, exports, require) {\n%s\n};\n" % (json.dumps(name), src))
@@ -293,12 +325,12 @@ def bundle():
     return "\n".join(parts)
 
 
-def run_js(driver, timeout=600):
+def run_js(driver, timeout=600, files=None):
     """Run bundle + driver under oracle/_ref/js; returns stdout."""
     if not available():
         raise RuntimeError("reference JS engine unavailable (need %s and %s)" % (REF, JS))
     with tempfile.NamedTemporaryFile("w", suffix=".js", delete=False) as f:
-        f.write(bundle())
+        f.write(bundle(files))
         f.write("\n")
         f.write(driver)
         path = f.name
@@ -340,6 +372,87 @@ def decode_sessions(sessions):
     lines.append("];\nfor (var i = 0; i < SESS.length; ++i) print(decodeSession(SESS[i]));")
     out = run_js("\n".join(lines))
     return [_decanon(json.loads(l)) for l in out.splitlines() if l.strip()]
+
+
+SESSION_DRIVER = r"""
+var zksession = requireShim('./zk-session');
+
+/* Decode one server->client stream with the reference decoder and hand every packet that
+ * comes out after the handshake to the handler ZKSession.state_attached registers for its
+ * connection's 'packet' event (lib/zk-session.js:227-236), on a bare object that has just
+ * the members that handler and processNotification (:389-419) touch. */
+function sessionFold(sess, untilError) {
+	var handled = 0;
+	var fsm = {
+		zcf_xidMap: sess.xidMap || {},
+		isInState: function (st) { return (st === 'handshaking' && handled < sess.hs); }
+	};
+	var ds = new zkstreams.ZKDecodeStream({ fsm: fsm, isServer: false });
+	var counts = {}, ignored = 0, threw = 0, replies = 0, stopped = false;
+	var self = {
+		zs_lastZxid: undefined,
+		zs_conn: {}, zs_expiryTimer: {},
+		zs_log: { warn: function () { ignored++; }, trace: function () {} },
+		zs_watchers: {},
+		zs_collector: { getCollector: function () {
+			return ({ increment: function (l) { counts[l.event] = (counts[l.event] || 0) + 1; } });
+		} },
+		resetExpiryTimer: function () {},
+		processNotification: zksession.ZKSession.prototype.processNotification
+	};
+	var handler;
+	var S = { on: function (em, ev, fn) { if (em === self.zs_conn && ev === 'packet') handler = fn; },
+	    gotoState: function () {} };
+	zksession.ZKSession.prototype.state_attached.call(self, S);
+	var seen = 0, dead = false;
+	function drain() {
+		while (seen < ds._events.length) {
+			var e = ds._events[seen++];
+			if (e.push !== undefined) {
+				var wasHandshake = (handled < sess.hs);
+				handled++;
+				if (wasHandshake || stopped) continue;
+				var before = self.zs_lastZxid;
+				if (e.push.opcode !== 'NOTIFICATION') replies++;
+				try { handler(e.push); } catch (ex) { threw++; }
+			} else if (e.ev === 'error') {
+				if (e.arg.code === 'BAD_LENGTH') dead = true; else handled++;
+				if (untilError) stopped = true;
+			}
+		}
+	}
+	var opush = ds.push, oemit = ds.emit;
+	ds.push = function (x) { opush.call(ds, x); drain(); };
+	ds.emit = function (ev, a) { oemit.call(ds, ev, a); drain(); };
+	for (var i = 0; i < sess.chunks.length && !dead; ++i) {
+		var called = false;
+		ds._transform(hex(sess.chunks[i]), null, function () { called = true; });
+		drain();
+		if (!called) dead = true;
+	}
+	var z = self.zs_lastZxid, zhex = null;
+	if (z !== undefined) { zhex = ''; for (var k = 0; k < z._b.length; ++k) { var h = (z._b[k] & 0xff).toString(16); zhex += (h.length < 2 ? '0' : '') + h; } }
+	var cs = [];
+	for (var ev in counts) cs.push(jstr(ev) + ':' + counts[ev]);
+	return '{"maxZxid":' + (zhex === null ? 'null' : '"' + zhex + '"') + ',"replies":' + replies +
+	    ',"counts":{' + cs.join(',') + '},"ignored":' + ignored + ',"threw":' + threw + '}';
+}
+"""
+
+
+def session_folds(sessions, until_error=False):
+    """Run the reference's own ZKSession packet handler over client-side sessions (as for
+    decode_sessions).  zs_lastZxid starts undefined here (not 0) so the result is the plain
+    maximum.  Returns per session dict(maxZxid=hex|None, replies, counts={event:n}, ignored, threw)."""
+    lines = [SESSION_DRIVER, "var SESS = ["]
+    for s in sessions:
+        xm = ",".join("%s:%s" % (json.dumps(str(k)), json.dumps(v)) for k, v in s.get("xidMap", {}).items())
+        chunks = ",".join(json.dumps(bytes(c).hex()) for c in s["chunks"])
+        lines.append("{hs:%d,xidMap:{%s},chunks:[%s]}," % (s.get("hs", 1), xm, chunks))
+    lines.append("];\nfor (var i = 0; i < SESS.length; ++i) print(sessionFold(SESS[i], %s));" % (
+        "true" if until_error else "false"))
+    out = run_js("\n".join(lines), files=REF_FILES + ["zk-session"])
+    return [json.loads(l) for l in out.splitlines() if l.strip()]
 
 
 def js_literal(v):

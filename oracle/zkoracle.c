@@ -693,6 +693,51 @@ int zko_xidtab_build(const zkb_decoded *req, uint32_t nsessions, const zkb_xidta
 }
 
 /* ------------------------------------------------------------------------------ */
+/* ZKSession's per-packet folds (lib/zk-session.js:227-236, :389-419), packet by packet */
+
+int zko_session_stats(const zkb_decoded *dec, uint32_t nsessions, uint32_t flags, zkb_session_stats *out)
+{
+	uint8_t *dead = calloc(nsessions ? nsessions : 1, 1);   /* connection torn down after a decoder error */
+	for (uint32_t s = 0; s < nsessions; s++) {
+		out->max_zxid[s] = INT64_MIN;
+		out->n_replies[s] = 0;
+		for (int k = 0; k < ZKB_NOTIFY_SLOTS; k++) out->notifications[(size_t)s * ZKB_NOTIFY_SLOTS + k] = 0;
+	}
+	for (uint64_t f = 0; f < dec->n_frames; f++) {
+		uint32_t m = dec->meta[f];
+		uint32_t s = dec->session[f];
+		if (s >= nsessions) continue;
+		if (ZKB_META_STATUS(m) != ZKB_ST_OK) {
+			/* 'error' on the decoder: connection-fsm.js:234-239 moves the connection to 'error' */
+			if (flags & ZKB_STATS_UNTIL_ERROR) dead[s] = 1;
+			continue;
+		}
+		if (dead[s]) continue;
+		/* only packets read with readResponse reach the attached session's handler; the
+		 * connect response is consumed by state_attaching (zk-session.js:170-190) */
+		if (ZKB_META_KIND(m) != ZKB_KIND_RESPONSE) continue;
+		if (ZKB_META_OPCODE(m) != ZKB_OP_NOTIFICATION) {
+			/* :229-235 — BigInteger(pkt.zxid).compareTo(zs_lastZxid) > 0, signed */
+			if (out->n_replies[s] == 0 || dec->zxid[f] > out->max_zxid[s]) out->max_zxid[s] = dec->zxid[f];
+			out->n_replies[s]++;
+			continue;
+		}
+		/* processNotification :389-419.  readResponse reads the body only when err is OK
+		 * (zk-buffer.js:296), so an error reply has no pkt.state */
+		int slot;
+		if (dec->err[f] != 0 || dec->a1[f] != 3 /* STATE.SYNC_CONNECTED, zk-consts.js:124 */)
+			slot = ZKB_NOTIFY_IGNORED;
+		else if (dec->a0[f] >= 1 && dec->a0[f] <= 4)   /* NOTIFICATION_TYPE, zk-consts.js:111-116 */
+			slot = dec->a0[f];
+		else
+			slot = ZKB_NOTIFY_BAD_TYPE;                 /* pkt.type undefined: :402 throws */
+		out->notifications[(size_t)s * ZKB_NOTIFY_SLOTS + slot]++;
+	}
+	free(dead);
+	return 0;
+}
+
+/* ------------------------------------------------------------------------------ */
 /* JuteBuffer write side + ZKBuffer writers                                       */
 
 typedef struct { uint8_t *p; uint64_t n, cap; } wbuf_t;

@@ -49,6 +49,9 @@ def load():
                                          C.POINTER(C.c_uint64)]
         lib.zko_xidtab_build.restype = C.c_int
         lib.zko_xidtab_build.argtypes = [C.POINTER(_abi.Decoded), C.c_uint32, C.POINTER(_abi.XidTab), P]
+        lib.zko_session_stats.restype = C.c_int
+        lib.zko_session_stats.argtypes = [C.POINTER(_abi.Decoded), C.c_uint32, C.c_uint32,
+                                          C.POINTER(_abi.SessionStats)]
         lib.zko_encode.restype = C.c_int
         lib.zko_encode.argtypes = [C.POINTER(_abi.Requests), C.POINTER(P), C.POINTER(C.c_uint64), P, P]
         lib.zko_buf_free.argtypes = [P]
@@ -101,6 +104,18 @@ def xidtab_build(req_cols, layout):
     ops = np.empty(layout.nops, dtype=np.int8)
     lib.zko_xidtab_build(C.byref(d), len(layout.count), C.byref(t), ops.ctypes.data if ops.size else None)
     return zk.XidTable(layout.base, layout.count, ops)
+
+
+def session_stats(cols, nsessions, flags=0):
+    """ZKSession's per-packet folds over decoded response columns -> zk.SessionStats."""
+    lib = load()
+    d = _abi.Decoded()
+    d.n_frames = cols.n_frames
+    for name in ("meta", "session", "zxid", "err", "a0", "a1"):
+        setattr(d, name, getattr(cols, name).ctypes.data)
+    st = zk.SessionStats.empty(nsessions)
+    lib.zko_session_stats(C.byref(d), nsessions, flags, C.byref(st.struct()))
+    return st
 
 
 def encode(req):

@@ -88,3 +88,38 @@ print('{' + o.join(',') + ',"arena":"' + ar + '"}');
             if name in ("zxid", "zxid2"):
                 want = want.view(np.int32)
             assert [int(x) for x in want] == got[name], (name, pkt)
+
+
+def test_js_session_fold_matches_reference_handler(oracle, synth, zk):
+    """js/session-fold.js applied to the oracle's reductions leaves a session where the
+    reference's own packet handler left it (tests/golden/ref_session_folds.json)."""
+    g = json.load(open(os.path.join(GOLD, "ref_session_folds.json")))["sessions"]
+    c = synth.Corpus()
+    for s in g:
+        c.add(bytes.fromhex(s["hex"]), hs=s["hs"], xidmap={int(k): v for k, v in s["xidMap"].items()})
+    d, off, fl, hs = c.arrays()
+    cols = oracle.decode(d, off, fl, hs, c.xidtable())
+    st = oracle.session_stats(cols, len(g), 0)
+    parts = ["var stats = {n_replies: %s, max_zxid: %s, notifications: %s};" % (
+        js_array(st.n_replies), js_array64(st.max_zxid), js_array(st.notifications.reshape(-1)))]
+    parts.append(open(os.path.join(ROOT, "node-zkstream_b200", "js", "session-fold.js")).read())
+    parts.append(r"""
+var fold = makeSessionFold({ BigInteger: BigInteger, consts: requireShim('./zk-consts') });
+for (var s = 0; s < %d; ++s) {
+	var counts = {};
+	var session = { zs_lastZxid: undefined, zs_collector: { getCollector: function () {
+		return ({ increment: function (l) { counts[l.event] = (counts[l.event] || 0) + 1; } }); } } };
+	fold(session, stats, s);
+	var z = session.zs_lastZxid, zhex = null;
+	if (z !== undefined) { zhex = ''; for (var k = 0; k < 8; ++k) { var h = (z._b[k] & 0xff).toString(16); zhex += (h.length < 2 ? '0' : '') + h; } }
+	var cs = [];
+	for (var ev in counts) cs.push(jstr(ev) + ':' + counts[ev]);
+	print('{"maxZxid":' + (zhex === null ? 'null' : '"' + zhex + '"') + ',"counts":{' + cs.join(',') + '}}');
+}
+""" % len(g))
+    out = ref_js.run_js("\n".join(parts))
+    lines = [json.loads(l) for l in out.splitlines() if l.strip()]
+    assert len(lines) == len(g)
+    for got, ref in zip(lines, g):
+        assert got["maxZxid"] == ref["all"]["maxZxid"]
+        assert got["counts"] == ref["all"]["counts"]
