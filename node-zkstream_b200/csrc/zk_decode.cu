@@ -8,21 +8,24 @@
  *
  * Pipeline (all on the context's stream):
  *   k_split<SPEC>   one thread per splitter granule walks the length-prefix chain
- *                   (zk-streams.js:47-64) from a *guessed* entry point.  The walk only
- *                   touches the 4-byte prefixes, so it reads a few % of the batch.
+ *                   (zk-streams.js:47-64) from a *guessed* entry point and records, besides
+ *                   its exit and frame count, where the chain first stands inside every
+ *                   256-byte sub-range of the granule.  Only frame headers are touched.
  *   k_scan_*        a prefix scan over granules carries every granule's exit position to
  *                   its successors and sums frame counts; a granule whose guess disagrees
  *                   with what its predecessors say is marked dirty.
- *   k_split<FIX>    dirty granules re-walk from the carried position; repeat until no
- *                   granule is dirty.  By induction from granule 0 (whose entry is a
- *                   session start) the result is then exactly the sequential split.
- *   k_split<EMIT>   writes frame_off / frame_len / session rows and the per-session
- *                   consumed / bad_length_at / first_frame results.
- *   k_decode        one CTA per 32 KiB tile: stages the tile in shared memory with 16-byte
- *                   coalesced loads, one thread per frame parses the schema chosen by
- *                   kind/opcode, writes the FRAMES columns, and places STAT/BUF/ACL rows
- *                   through a decoupled look-back over per-tile row counts, so the input
- *                   is read from HBM once and the side tables come out dense and ordered.
+ *   k_split<FIX>    a dirty granule with a trustworthy carried position re-walks from it and
+ *                   carries the corrected chain on through the granules that follow until it
+ *                   merges with what is already recorded; scan again; repeat until no granule
+ *                   is dirty (one round on ordinary traffic).  By induction from each session
+ *                   start the result is then exactly the sequential split.
+ *   k_decode        one warp per 8 KiB chunk (four per CTA): TMA bulk copy of the chunk into
+ *                   shared memory; each lane walks the chain through its own 256-byte
+ *                   sub-range to place the frame starts; lane k parses frames k, k+32, ... with
+ *                   the schema chosen by kind/opcode and writes all FRAMES columns; STAT/BUF/ACL
+ *                   rows are recorded as bitmap bits and placed through a decoupled look-back
+ *                   over per-chunk row counts, so the input is read from HBM once and the side
+ *                   tables come out dense and ordered.
  */
 #include "zk_internal.h"
 
@@ -662,7 +665,6 @@ struct DecArgs {
 	const uint64_t *sess_off;
 	uint32_t        nsess;
 	const uint32_t *g_base;       /* per granule: first frame index */
-	const uint64_t *g_carry;      /* per granule: where the chain stands on entry */
 	const uint32_t *g_sf;         /* per granule: first session starting at or after it */
 	const uint32_t *g_ssrc;       /* per granule: 1 + last earlier granule with a session start */
 	const uint32_t *g_openlocal;  /* [version][g] */
@@ -2102,7 +2104,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		da.xt_base = xid->base; da.xt_count = xid->count; da.xt_off = xid->off; da.xt_ops = xid->ops;
 	}
 	da.sess_off = sess->off; da.nsess = nsess;
-	da.g_base = sa.g_base; da.g_carry = sa.g_carry; da.g_sf = sa.g_sf; da.g_ssrc = sa.g_ssrc;
+	da.g_base = sa.g_base; da.g_sf = sa.g_sf; da.g_ssrc = sa.g_ssrc;
 	da.g_openlocal = sa.g_openlocal; da.g_sub = sa.g_sub; da.g_sel = sa.g_sel;
 	da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_chunks = L.n_chunks;
 	da.n_frames = n_frames; da.o = *out;
