@@ -176,6 +176,95 @@ class RequestBatch:
         self.cols["acl_id_len"] = np.array([a[4] for a in acl], dtype=np.int32)
         return self
 
+    @classmethod
+    def from_columns(cls, cols, data):
+        """Decoded client->server frames back into encode descriptors: what a proxy or a capture
+        rewriter does between a ZKDecodeStream({isServer: true}) and a ZKEncodeStream.  `cols`
+        is the result of decoding `data` with ZKB_SESS_SERVER; every frame the reference would
+        have handed on as a packet (OK requests and ConnectRequests) becomes one row, plus the
+        header-only PING / CLOSE_SESSION frames, which readRequest rejects (zk-buffer.js:91-92)
+        but writeRequest writes (:129-132).  The arena is `data` itself: nothing is copied.
+        Returns (batch, frame index per row)."""
+        st, kind, op = cols.status, cols.kind, cols.opcode
+        req = (st == _abi.ST_OK) & (kind == _abi.KIND_REQUEST)
+        con = (st == _abi.ST_OK) & (kind == _abi.KIND_CONNECT_REQUEST)
+        hdr_only = ((st == _abi.ST_BAD_DECODE) & (kind == _abi.KIND_REQUEST) & (cols.frame_len == 8) &
+                    ((cols.detail & 7) == _abi.CAUSE_UNSUPPORTED) &
+                    ((op == OP_CODES["PING"]) | (op == OP_CODES["CLOSE_SESSION"])))
+        idx = np.nonzero(req | con | hdr_only)[0]
+        n = len(idx)
+        rows = {name: np.zeros(n, dtype=dt) for name, dt in _abi.REQ_COLS}
+        o = op[idx].astype(np.int8)
+        is_con = con[idx]
+        rows["op"] = np.where(is_con, np.int8(_abi.ENC_CONNECT_REQUEST), o).astype(np.int8)
+        rows["xid"] = np.where(is_con, 0, cols.xid[idx]).astype(np.int32)
+        # scalar fields (include/zkbatch.h, FRAMES columns by kind)
+        rows["a0"] = np.where(is_con, cols.xid[idx], cols.a0[idx]).astype(np.int32)
+        rows["a1"] = np.where(is_con, cols.err[idx], 0).astype(np.int32)
+        rows["zxid"] = cols.zxid[idx].astype(np.int64)
+        last = (cols.a0[idx].astype(np.int64) << 32) | (cols.a1[idx].astype(np.int64) & 0xFFFFFFFF)
+        rows["zxid2"] = np.where(is_con, last, 0).astype(np.int64)
+        # buffers: a frame's BUF rows are contiguous and in read order
+        b0 = np.searchsorted(cols.buf_frame, idx, "left")
+        has_path = np.isin(o, [OP_CODES[k] for k in ("GET_CHILDREN", "GET_CHILDREN2", "GET_DATA", "EXISTS", "CREATE",
+                                                      "DELETE", "GET_ACL", "SYNC", "SET_DATA")]) & ~is_con & ~hdr_only[idx]
+        has_data = np.isin(o, [OP_CODES["CREATE"], OP_CODES["SET_DATA"]]) & ~is_con
+        nb = max(cols.n_buf, 1)
+        boff = cols.buf_off if cols.n_buf else np.zeros(1, np.uint64)
+        blen = cols.buf_len if cols.n_buf else np.zeros(1, np.int32)
+        pr = np.minimum(b0, nb - 1)
+        rows["path_off"] = np.where(has_path, boff[pr], 0).astype(np.uint64)
+        rows["path_len"] = np.where(has_path, blen[pr], 0).astype(np.int32)
+        dr = np.minimum(np.where(is_con, b0, b0 + 1), nb - 1)
+        rows["data_off"] = np.where(has_data | is_con, boff[dr], 0).astype(np.uint64)
+        rows["data_len"] = np.where(has_data | is_con, blen[dr], 0).astype(np.int32)
+        # CREATE: its ACL rows; scheme and id are the BUF rows after path and data
+        is_create = (o == OP_CODES["CREATE"]) & ~is_con
+        a_first = np.searchsorted(cols.acl_frame, idx, "left")
+        rows["vec_first"] = np.where(is_create, a_first, 0).astype(np.uint32)
+        rows["vec_count"] = np.where(is_create, np.maximum(cols.a1[idx], 0), 0).astype(np.int32)
+        self = cls()
+        if cols.n_acl:
+            row_of_frame = np.full(cols.n_frames, -1, np.int64)
+            row_of_frame[idx] = np.arange(n)
+            r = row_of_frame[cols.acl_frame]
+            j = np.arange(cols.n_acl) - a_first[r]
+            srow = b0[r] + 2 + 2 * j
+            self.cols_acl = dict(acl_perms=cols.acl_perms.astype(np.int32),
+                                 acl_scheme_off=boff[srow].astype(np.uint64), acl_scheme_len=blen[srow].astype(np.int32),
+                                 acl_id_off=boff[srow + 1].astype(np.uint64), acl_id_len=blen[srow + 1].astype(np.int32))
+        else:
+            self.cols_acl = dict(acl_perms=np.zeros(0, np.int32), acl_scheme_off=np.zeros(0, np.uint64),
+                                 acl_scheme_len=np.zeros(0, np.int32), acl_id_off=np.zeros(0, np.uint64),
+                                 acl_id_len=np.zeros(0, np.int32))
+        # SET_WATCHES: all of the frame's BUF rows are its three path vectors back to back
+        is_sw = (o == OP_CODES["SET_WATCHES"]) & ~is_con
+        c0 = np.maximum(cols.a0[idx], 0)
+        c1 = np.maximum(cols.a1[idx], 0)
+        c2 = np.maximum(cols.err[idx], 0)
+        tot = np.where(is_sw, c0 + c1 + c2, 0).astype(np.int64)
+        e_first = np.cumsum(tot) - tot
+        rows["vec_first"] = np.where(is_sw, e_first, rows["vec_first"]).astype(np.uint32)
+        rows["vec_count"] = np.where(is_sw, tot, rows["vec_count"]).astype(np.int32)
+        rows["n0"] = np.where(is_sw, c0, 0).astype(np.int32)
+        rows["n1"] = np.where(is_sw, c1, 0).astype(np.int32)
+        if is_sw.any():
+            sw_frame = np.zeros(cols.n_frames, bool)
+            sw_frame[idx[is_sw]] = True
+            m = sw_frame[cols.buf_frame]
+            elem_off, elem_len = cols.buf_off[m].astype(np.uint64), cols.buf_len[m].astype(np.int32)
+        else:
+            elem_off, elem_len = np.zeros(0, np.uint64), np.zeros(0, np.int32)
+        self.n = n
+        self.cols = rows
+        self.cols.update(self.cols_acl)
+        del self.cols_acl
+        self.cols["elem_off"], self.cols["elem_len"] = elem_off, elem_len
+        self.n_elem, self.n_acl = len(elem_off), int(cols.n_acl)
+        self.arena = np.ascontiguousarray(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+        self.names = None
+        return self, idx
+
     def struct(self, ptr=lambda a: a.ctypes.data if a.size else None):
         """(zkb_requests struct with host pointers, objects to keep alive)."""
         r = _abi.Requests()

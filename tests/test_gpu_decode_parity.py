@@ -215,3 +215,70 @@ def test_sessions_aligned_to_chunk_and_subrange_edges(ctx, oracle, synth):
     g, o = both(ctx, oracle, c)
     assert g.diff(o) == []
     assert (g.status == 0).all()
+
+
+def test_cfg3_full_size_one_giant_session(ctx, oracle, synth, zk):
+    """Config 3 at BASELINE size: one 1.1 GB session of 32 M tiny frames (20-44 bytes), so the
+    splitter has nothing but guesses to go on.  Known structure at full size, the oracle on a
+    100 MB prefix."""
+    n = 32_000_000
+    data = synth.native_cfg3(7, n)
+    assert data.size > 1_000_000_000
+    cols = ctx.decode_host(data, None, None, None, None)
+    assert cols.n_frames == n + 1 and (cols.status == 0).all()
+    assert int(cols.sess_consumed[0]) == data.size and int(cols.sess_bad_length_at[0]) == zk._abi.NO_OFFSET
+    op = cols.opcode[1:]
+    note = op == 0
+    assert ((op == 0) | (op == 11)).all() and 0.66 < note.mean() < 0.67
+    assert (cols.xid[1:][note] == -1).all() and (cols.zxid[1:][note] == -1).all() and (cols.xid[1:][~note] == -2).all()
+    assert cols.n_buf == int(note.sum()) + 1 and cols.n_stat == 0 and cols.n_acl == 0
+    assert np.array_equal(cols.buf_frame[1:], np.nonzero(note)[0].astype(np.uint32) + 1)   # one path per notification
+    assert (cols.frame_len[1:][~note] == 16).all()
+    assert np.array_equal(cols.frame_len[1:][note], 28 + cols.buf_len[1:])
+    assert (cols.buf_len[1:] >= 4).all() and (cols.buf_len[1:] <= 12).all()
+    assert np.array_equal(cols.buf_off[1:], cols.frame_off[1:][note] + 32)
+    assert np.array_equal(np.diff(cols.frame_off.astype(np.int64)), cols.frame_len[:-1].astype(np.int64) + 4)
+    assert ((cols.a0[1:][note] >= 1) & (cols.a0[1:][note] <= 4) & (cols.a1[1:][note] == 3)).all()
+    # the session folds at this size
+    st = ctx.session_stats_host(cols)
+    assert int(st.n_replies[0]) == int((~note).sum())
+    assert int(st.max_zxid[0]) == int(cols.zxid[1:][~note].max())
+    assert [int(x) for x in st.notifications[0]] == [0] + [int((cols.a0[1:][note] == t).sum()) for t in (1, 2, 3, 4)] + [0]
+    # full parity on a prefix
+    cut = int(cols.frame_off[3_000_001])
+    g = ctx.decode_host(data[:cut], None, None, None, None)
+    o = oracle.decode(data[:cut], None, None, None, None)
+    assert g.diff(o) == [] and g.n_frames == 3_000_001
+
+
+def test_cfg4_full_size_large_znodes(ctx, oracle, synth, zk):
+    """Config 4 at BASELINE size: 1 000 000-byte payloads and 10^4-10^5-child vectors, 8 GB.
+    One ~40 MB session is checked against the oracle; ~210 copies of it side by side must each
+    decode to the same rows."""
+    c = synth.cfg4_large(40, seed=44)
+    one = np.frombuffer(c.data, dtype=np.uint8)
+    xt1 = c.xidtable()
+    g1 = ctx.decode_host(one, None, None, None, xt1)
+    assert g1.diff(oracle.decode(one, None, None, None, xt1)) == []
+    assert (g1.status == 0).all() and g1.n_frames == 41
+    reps = 8_000_000_000 // one.size + 1
+    data = np.tile(one, reps)
+    assert data.size > 8_000_000_000
+    off = np.arange(reps + 1, dtype=np.uint64) * np.uint64(one.size)
+    xt = zk.XidTable.from_maps([c.xidmaps[0]] * reps)
+    cols = ctx.decode_host(data, off, None, None, xt, copy=False)
+    F, B, S = g1.n_frames, g1.n_buf, g1.n_stat
+    assert cols.n_frames == reps * F and cols.n_buf == reps * B and cols.n_stat == reps * S
+    assert (cols.status == 0).all()
+    base = off[:-1].astype(np.int64)
+    for name in ("frame_len", "meta", "xid", "zxid", "err", "a0", "a1"):
+        assert (getattr(cols, name).reshape(reps, F) == getattr(g1, name)[None, :]).all(), name
+    assert (cols.frame_off.astype(np.int64).reshape(reps, F) - base[:, None] == g1.frame_off.astype(np.int64)[None, :]).all()
+    assert (cols.session.reshape(reps, F) == np.arange(reps, dtype=np.uint32)[:, None]).all()
+    assert (cols.buf_len.reshape(reps, B) == g1.buf_len[None, :]).all()
+    assert (cols.buf_off.astype(np.int64).reshape(reps, B) - base[:, None] == g1.buf_off.astype(np.int64)[None, :]).all()
+    assert (cols.buf_frame.astype(np.int64).reshape(reps, B) - (np.arange(reps) * F)[:, None] == g1.buf_frame[None, :]).all()
+    for name in ("czxid", "mzxid", "ctime", "mtime", "version", "dataLength", "numChildren", "pzxid"):
+        assert (getattr(cols, name).reshape(reps, S) == getattr(g1, name)[None, :]).all(), name
+    assert (cols.sess_consumed.astype(np.int64) == base + one.size).all()
+    assert np.array_equal(cols.sess_first_frame, np.arange(reps + 1, dtype=np.uint32) * F)

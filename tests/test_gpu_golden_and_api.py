@@ -302,3 +302,35 @@ def test_replay_host_pipelined_matches_oracle(ctx, oracle, synth):
         assert req.diff(want_req) == [], slice_bytes
         assert rsp.diff(want_rsp) == [], slice_bytes
     assert (want_rsp.status == 0).all()
+
+
+def test_reencode_round_trip_at_scale(ctx, synth):
+    """Config 5's encode half: ~3.2 M requests (830 MB) decoded on the GPU, turned back into
+    encode descriptors (RequestBatch.from_columns) and encoded on the GPU must reproduce the wire
+    bytes — up to the two places where the reference's writers differ from what a server-side
+    peer may send: empty buffers are written as length -1 (jute-buffer.js:127-130) and the
+    ConnectRequest's trailing readOnly byte is not written (zk-buffer.js:32-39)."""
+    pc = synth.native_cfg2(31, 160, 20000)
+    cols = ctx.decode_host(pc.req, pc.req_off, pc.req_flags, None, None)
+    rb, idx = zk.RequestBatch.from_columns(cols, pc.req)
+    assert rb.n == cols.n_frames == 160 * 20001
+    enc, fo, st = ctx.encode_host(rb)
+    assert (st == 0).all()
+    want = pc.req.copy()
+    # empty buffers: the generator writes length 0, the reference's writer -1
+    empty = np.nonzero(cols.buf_len == 0)[0]
+    pos = cols.buf_off[empty].astype(np.int64) - 4
+    was_zero = (want[pos] == 0) & (want[pos + 1] == 0) & (want[pos + 2] == 0) & (want[pos + 3] == 0)
+    for k in range(4):
+        want[pos[was_zero] + k] = 0xFF
+    # connect frames: drop the readOnly byte, shorten the prefix by one
+    first = cols.sess_first_frame[:-1].astype(np.int64)
+    assert (cols.kind[first] == zk._abi.KIND_CONNECT_REQUEST).all()
+    foff = cols.frame_off[first].astype(np.int64)
+    flen = cols.frame_len[first].astype(np.int64)
+    for k in range(4):
+        want[foff + k] = ((flen - 1) >> (8 * (3 - k))) & 0xFF
+    want = np.delete(want, foff + 4 + flen - 1)
+    assert enc.size == want.size
+    assert np.array_equal(enc, want)
+    assert int(fo[-1]) == enc.size
