@@ -1179,13 +1179,44 @@ struct FC {
 		cur += 68;
 		return true;
 	}
+	/* bits gathered for one bitmap word go to shared memory with one atomic per bitmap */
+	template <int M>
+	__device__ __forceinline__ void flush(uint32_t w, uint32_t am, uint32_t a0, uint32_t a1)
+	{
+		if (!am) return;
+		if (M == FAST_MARK) {
+			atomicOr(&c->m_buf[w], am);
+			if (a0) atomicOr(&c->sub0[w], a0);
+			if (a1) atomicOr(&c->sub1[w], a1);
+		} else {
+			atomicAnd(&c->m_buf[w], ~am);
+			atomicAnd(&c->sub0[w], ~am);
+			atomicAnd(&c->sub1[w], ~am);
+		}
+	}
+	/* vector<ustring>: neighbouring elements usually share a bitmap word (128 input bytes) */
 	template <int M>
 	__device__ __forceinline__ bool strvec(int32_t &n)
 	{
 		int32_t count;
 		if (!i32(count)) return false;
-		for (int32_t i = 0; i < count; ++i)
-			if (!buf<M>(c->m_buf)) return false;
+		uint32_t cw = 0, am = 0, a0 = 0, a1 = 0;
+		bool ok = true;
+		for (int32_t i = 0; i < count; ++i) {
+			if (cur + 4 > size) { ok = false; break; }
+			const int32_t l = (int32_t)sm_be32(c->tile, pr + cur);
+			const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+			if (cur + 4 + ul > size) { ok = false; break; }
+			const uint32_t prel = pr + cur;
+			const uint32_t w = prel >> 7, bit = 1u << ((prel >> 2) & 31);
+			if (w != cw) { flush<M>(cw, am, a0, a1); cw = w; am = a0 = a1 = 0; }
+			am |= bit;
+			if (prel & 1) a0 |= bit;
+			if (prel & 2) a1 |= bit;
+			cur += 4 + ul;
+		}
+		flush<M>(cw, am, a0, a1);
+		if (!ok) return false;
 		n = count > 0 ? count : 0;
 		return true;
 	}

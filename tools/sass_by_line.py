@@ -20,9 +20,10 @@ cur = 0
 for l in lines[start + 1:]:
     if l.startswith("\t.section") or l.startswith(".text."):
         break
-    m = re.search(r'//## File ".*?", line (\d+)(.*)', l)
+    m = re.search(r'//## File "(.*?)", line (\d+)', l)
     if m:
-        cur = int(m.group(1))
+        f = m.group(1)
+        cur = int(m.group(2)) if f.endswith("zk_decode.cu") else (f.split("/")[-1], int(m.group(2)))
         continue
     if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+\S", l):
         ins.append(cur)
@@ -61,5 +62,8 @@ print("total warp inst %d, thread inst %d (%.1f/32), samples %d" % (tot[0], tot[
 src = open("node-zkstream_b200/csrc/zk_decode.cu").read().split("\n")
 print("%6s %7s %7s %5s  %s" % ("line", "inst%", "smpl%", "thr", "source"))
 for ln, p in sorted(per.items(), key=lambda kv: -kv[1][0])[:70]:
-    print("%6d %6.2f%% %6.2f%% %5.1f  %s" % (ln, 100.0 * p[0] / tot[0], 100.0 * p[2] / max(tot[2], 1), p[1] / max(p[0], 1),
-                                           src[ln - 1].strip()[:110] if 0 < ln <= len(src) else ""))
+    if isinstance(ln, tuple):
+        label, text = "hdr", "%s:%d" % ln
+    else:
+        label, text = str(ln), (src[ln - 1].strip()[:110] if 0 < ln <= len(src) else "")
+    print("%6s %6.2f%% %6.2f%% %5.1f  %s" % (label, 100.0 * p[0] / tot[0], 100.0 * p[2] / max(tot[2], 1), p[1] / max(p[0], 1), text))
