@@ -282,3 +282,49 @@ def test_cfg4_full_size_large_znodes(ctx, oracle, synth, zk):
         assert (getattr(cols, name).reshape(reps, S) == getattr(g1, name)[None, :]).all(), name
     assert (cols.sess_consumed.astype(np.int64) == base + one.size).all()
     assert np.array_equal(cols.sess_first_frame, np.arange(reps + 1, dtype=np.uint32) * F)
+
+
+def test_half_a_million_tiny_sessions(ctx, oracle, synth):
+    """600 000 sessions of 0-3 frames (hundreds of session starts per 8 KiB chunk, a third of the
+    sessions empty, some cut mid-frame): session lookup beyond the 32 boundaries a warp keeps in
+    registers, first_frame / consumed bookkeeping for sessions that start and end inside one lane's
+    sub-range."""
+    import random
+    rng = random.Random(77)
+    ping = synth.frame(synth.resp_header(-2, 9, 0))
+    note = synth.frame(synth.resp_header(-1, -1, 0) + synth.be32(3) + synth.be32(3) + synth.jbuf(b"/abc"))
+    conn = synth.frame(synth.connect_response(rng))
+    kinds = [b"", b"", conn, conn + ping, conn + ping + note, conn + note[:7], ping + note, conn + ping + b"\x7f\xff\xff\xff"]
+    hs_of = [1, 1, 1, 1, 1, 1, 0, 1]
+    pick = np.frombuffer(bytes(rng.randrange(len(kinds)) for _ in range(600_000)), dtype=np.uint8)
+    lens = np.array([len(k) for k in kinds], dtype=np.uint64)[pick]
+    off = np.zeros(len(pick) + 1, dtype=np.uint64)
+    np.cumsum(lens, out=off[1:])
+    data = np.frombuffer(b"".join(kinds[i] for i in pick), dtype=np.uint8)
+    hs = np.array(hs_of, dtype=np.uint32)[pick]
+    g = ctx.decode_host(data, off, None, hs, None)
+    o = oracle.decode(data, off, None, hs, None)
+    assert g.diff(o) == []
+    assert g.n_frames > 700_000
+
+
+def test_maximum_frame_length(ctx, oracle, synth, zk):
+    """L == 16 MiB is the largest legal length (zk-streams.js:23,49: `len > 16 MiB` is the error);
+    one byte more is BAD_LENGTH and ends the session.  A 16 MiB GET_DATA reply spans 2049 chunks."""
+    import random
+    rng = random.Random(5)
+    M = zk._abi.MAX_PACKET
+    body_len = M - 16 - 4 - 68
+    big = synth.resp_header(1, 7, 0) + synth.jbuf(bytes(body_len)) + synth.stat_bytes(rng, body_len, 0)
+    assert len(big) == M
+    c = synth.Corpus()
+    c.add(synth.frame(synth.connect_response(rng)) + synth.frame(big) + synth.frame(synth.resp_header(-2, 8, 0)),
+          xidmap={1: 4})
+    c.add(synth.frame(synth.connect_response(rng)) + (M + 1).to_bytes(4, "big") + bytes(100), xidmap={})
+    c.add(synth.frame(synth.connect_response(rng)) + synth.frame(big)[:-1], xidmap={1: 4})     # one byte short: stays buffered
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+    assert g.n_frames == 5 and list(g.frame_len[:3]) == [len(synth.connect_response(rng)), M, 16]
+    assert int(g.buf_len[1]) == body_len and int(g.dataLength[0]) == body_len
+    assert int(g.sess_bad_length_at[1]) == int(g.sess_consumed[1]) and int(g.sess_bad_length_at[0]) == zk._abi.NO_OFFSET
+    assert int(g.sess_consumed[2]) == int(c.sess_off[2]) + 4 + len(synth.connect_response(rng))
