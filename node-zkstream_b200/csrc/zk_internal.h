@@ -33,7 +33,7 @@
 struct zk_ctrl {
 	unsigned int       error;
 	unsigned int       n_dirty;     /* granules whose state changed in the last scan (dirty or re-selected) */
-	unsigned int       ticket;
+	unsigned int       reserved0;   /* keeps n_dirty .. n_rewalk one 12-byte span (cleared together) */
 	unsigned int       n_rewalk;    /* of those, granules that need a new walk */
 	unsigned long long n_frames;
 	unsigned long long n_stat, n_buf, n_acl;

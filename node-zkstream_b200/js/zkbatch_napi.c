@@ -207,6 +207,47 @@ static napi_value encode_columns(napi_env env, napi_callback_info info)
 	return o;
 }
 
+/* sessionStats(ctx, cols, nsessions, flags): cols = a decodeHost result (response direction).
+ * Returns { n_replies: Uint32Array, max_zxid: Int32Array [lo, hi] pairs, notifications:
+ * Uint32Array[6 * nsessions] } for js/session-fold.js (zkb_session_stats_host). */
+static napi_value session_stats(napi_env env, napi_callback_info info)
+{
+	size_t argc = 4; napi_value argv[4];
+	zkb_ctx *ctx = NULL; uint32_t nsess = 1, flags = 0;
+	napi_get_cb_info(env, info, &argc, argv, NULL, NULL);
+	if (argc < 2) { napi_throw_error(env, NULL, "sessionStats(ctx, cols, nsessions, flags)"); return NULL; }
+	napi_get_value_external(env, argv[0], (void **)&ctx);
+	if (argc >= 3) napi_get_value_uint32(env, argv[2], &nsess);
+	if (argc >= 4) napi_get_value_uint32(env, argv[3], &flags);
+	zkb_decoded d;
+	size_t n = 0;
+	memset(&d, 0, sizeof (d));
+	d.meta = (uint32_t *)ta_ptr(env, argv[1], "meta", &n);
+	d.n_frames = n;
+	d.session = (uint32_t *)ta_ptr(env, argv[1], "session", NULL);
+	d.zxid = (int64_t *)ta_ptr(env, argv[1], "zxid", NULL);
+	d.a0 = (int32_t *)ta_ptr(env, argv[1], "a0", NULL);
+	d.a1 = (int32_t *)ta_ptr(env, argv[1], "a1", NULL);
+	napi_value o = NULL, ab = NULL, ta = NULL;
+	zkb_session_stats st;
+	void *p = NULL;
+	napi_create_object(env, &o);
+	napi_create_arraybuffer(env, (size_t)nsess * 8 + 8, &p, &ab); st.max_zxid = (int64_t *)p;
+	napi_create_typedarray(env, napi_int32_array, (size_t)nsess * 2, ab, 0, &ta);
+	napi_set_named_property(env, o, "max_zxid", ta);
+	napi_create_arraybuffer(env, (size_t)nsess * 4 + 8, &p, &ab); st.n_replies = (uint32_t *)p;
+	napi_create_typedarray(env, napi_uint32_array, nsess, ab, 0, &ta);
+	napi_set_named_property(env, o, "n_replies", ta);
+	napi_create_arraybuffer(env, (size_t)nsess * 4 * ZKB_NOTIFY_SLOTS + 8, &p, &ab); st.notifications = (uint32_t *)p;
+	napi_create_typedarray(env, napi_uint32_array, (size_t)nsess * ZKB_NOTIFY_SLOTS, ab, 0, &ta);
+	napi_set_named_property(env, o, "notifications", ta);
+	if (zkb_session_stats_host(ctx, &d, nsess, flags, &st) != ZKB_OK) {
+		napi_throw_error(env, "ZKB", zkb_last_error(ctx));
+		return NULL;
+	}
+	return o;
+}
+
 static napi_value init(napi_env env, napi_value exports)
 {
 	napi_value f = NULL;
@@ -216,6 +257,8 @@ static napi_value init(napi_env env, napi_value exports)
 	napi_set_named_property(env, exports, "decodeHost", f);
 	napi_create_function(env, "encodeColumns", NAPI_AUTO_LENGTH, encode_columns, NULL, &f);
 	napi_set_named_property(env, exports, "encodeColumns", f);
+	napi_create_function(env, "sessionStats", NAPI_AUTO_LENGTH, session_stats, NULL, &f);
+	napi_set_named_property(env, exports, "sessionStats", f);
 	return exports;
 }
 
