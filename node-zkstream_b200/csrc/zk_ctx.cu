@@ -75,6 +75,7 @@ ZKB_EXPORT void zkb_ctx_destroy(zkb_ctx *ctx)
 	cudaSetDevice(ctx->device);
 	if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
 	if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+	if (ctx->d_span) cudaFree(ctx->d_span);
 	if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
 	if (ctx->h_ctrl) cudaFreeHost(ctx->h_ctrl);
 	if (ctx->d_in) cudaFree(ctx->d_in);

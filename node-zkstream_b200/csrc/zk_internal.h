@@ -54,6 +54,7 @@ struct zkb_ctx {
 	unsigned int split_iters[32][2];  /* last split: (n_dirty, n_rewalk) after each scan */
 	/* device scratch (grown on demand, never shrunk) */
 	void         *d_scratch;   size_t d_scratch_bytes;
+	void         *d_span;      size_t d_span_bytes;    /* encoder: first packet of every output span */
 	zk_ctrl      *d_ctrl;
 	zk_ctrl      *h_ctrl;      /* pinned */
 	/* host-variant staging */

@@ -147,3 +147,36 @@ def session_stats_dev(ctx, dcols, nsess, flags=0, device="cuda:0"):
     ctx._check(ctx._lib.zkb_session_stats_dev(ctx._h, C.byref(dcols.struct), nsess, flags, C.byref(st)))
     return SessionStats(mx[:nsess].cpu().numpy().copy(), nr[:nsess].cpu().numpy().view(np.uint32).copy(),
                         nt[:nsess * _abi.NOTIFY_SLOTS].cpu().numpy().view(np.uint32).reshape(nsess, _abi.NOTIFY_SLOTS).copy())
+
+
+class DeviceRequests:
+    """A RequestBatch (encode.py) uploaded to HBM: arena and every descriptor column."""
+
+    def __init__(self, batch, device="cuda:0"):
+        self.n = batch.n
+        self.t = {"arena": to_device(batch.arena, device, pad=16)}
+        r = _abi.Requests()
+        r.n, r.arena_len, r.n_elem, r.n_acl = batch.n, batch.arena.size, batch.n_elem, batch.n_acl
+        r.arena = self.t["arena"].data_ptr()
+        for name, dt in _abi.REQ_COLS + _abi.ELEM_COLS + _abi.REQ_ACL_COLS:
+            self.t[name] = to_device(np.ascontiguousarray(batch.cols[name], dtype=_NP_DT[dt]), device)
+            setattr(r, name, self.t[name].data_ptr())
+        self.struct = r
+
+    def nbytes(self):
+        return sum(t.numel() for t in self.t.values())
+
+
+def encode_dev(ctx, dreq, out_cap, device="cuda:0", out=None):
+    """zkb_encode_dev into a device buffer of out_cap bytes.  Returns (out tensor, frame_off
+    tensor [n+1] int64, status tensor [n] uint8, out_len)."""
+    if out is None:
+        out = (torch.empty(out_cap + 16, dtype=torch.uint8, device=device),
+               torch.empty(dreq.n + 1, dtype=torch.int64, device=device),
+               torch.empty(max(dreq.n, 1), dtype=torch.uint8, device=device))
+    n = C.c_uint64()
+    rc = ctx._lib.zkb_encode_dev(ctx._h, C.byref(dreq.struct), out[0].data_ptr(), out_cap, out[1].data_ptr(),
+                                 out[2].data_ptr(), C.byref(n))
+    if rc not in (0, _abi.EOVERFLOW):
+        ctx._check(rc)
+    return out[0], out[1], out[2], int(n.value), rc

@@ -334,3 +334,39 @@ def test_reencode_round_trip_at_scale(ctx, synth):
     assert enc.size == want.size
     assert np.array_equal(enc, want)
     assert int(fo[-1]) == enc.size
+
+
+def test_encode_dev_matches_host_variant(ctx, oracle):
+    """zkb_encode_dev (descriptors and output in HBM) against zkb_encode_host and the oracle,
+    including the too-small-output answer."""
+    dev = importlib.import_module("node-zkstream_b200.device")
+    rng = random.Random(12)
+    pkts = []
+    for i in range(3000):
+        k = rng.randrange(6)
+        if k == 0:
+            pkts.append(dict(xid=i, opcode="SET_DATA", path="/p/%d" % i, data=bytes(rng.randrange(0, 300)), version=i))
+        elif k == 1:
+            pkts.append(dict(xid=i, opcode="CREATE", path="/c/%d" % i, data=bytes(rng.randrange(0, 40)),
+                             acl=[dict(id=dict(scheme="world", id="anyone"), perms=["read", "write"])] * rng.randrange(0, 3),
+                             flags=["EPHEMERAL"] if i % 2 else []))
+        elif k == 2:
+            pkts.append(dict(xid=i, opcode="GET_CHILDREN2", path="/", watch=bool(i & 1)))
+        elif k == 3:
+            pkts.append(dict(xid=-8, opcode="SET_WATCHES", relZxid=bytes(8),
+                             events=dict(dataChanged=["/a%d" % j for j in range(rng.randrange(0, 4))], childrenChanged=["/b"])))
+        elif k == 4:
+            pkts.append(dict(xid=-2, opcode="PING"))
+        else:
+            pkts.append(dict(xid=i, opcode="SET_ACL", path="/x"))          # unsupported: status 1, no bytes
+    batch = zk.RequestBatch.from_packets(pkts)
+    hd, ho, hs = ctx.encode_host(batch)
+    od, oo, os_ = oracle.encode(batch)
+    assert np.array_equal(hd, od) and np.array_equal(ho, oo) and np.array_equal(hs, os_)
+    dr = dev.DeviceRequests(batch)
+    out, fo, st, n, rc = dev.encode_dev(ctx, dr, hd.size)
+    assert rc == 0 and n == hd.size
+    assert np.array_equal(out[:n].cpu().numpy(), hd)
+    assert np.array_equal(fo.cpu().numpy().view(np.uint64), ho) and np.array_equal(st[:len(pkts)].cpu().numpy(), hs)
+    _, _, _, need, rc = dev.encode_dev(ctx, dr, hd.size - 1)
+    assert rc == zk._abi.EOVERFLOW and need == hd.size
