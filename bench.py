@@ -424,6 +424,43 @@ def run_ours(args, rank, local_rank, world):
         "clocks": clocks,
     }
 
+    # ---- the encode half of the path (rank 0, N=1 only): requests of the first sessions re-encoded
+    # from their decoded columns, descriptors and arena resident in HBM ----
+    if rank == 0 and world == 1 and not args.no_encode:
+        ns_enc = min(S, 160)
+        cut = int(pc.req_off[ns_enc])
+        sub = ctx.decode_host(pc.req[:cut], pc.req_off[:ns_enc + 1], pc.req_flags[:ns_enc], None, None)
+        rb, _ = zk.RequestBatch.from_columns(sub, pc.req[:cut])
+        dr = dev.DeviceRequests(rb, device)
+        out = None
+        for _ in range(3):
+            o0, o1, o2, enc_n, rc = dev.encode_dev(ctx, dr, cut, device=device, out=out)
+            out = (o0, o1, o2)
+            assert rc == 0
+        l0 = ctx.kernel_launches
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(ext):
+            ev0.record()
+            for _ in range(5):
+                dev.encode_dev(ctx, dr, cut, device=device, out=out)
+            ev1.record()
+        torch.cuda.synchronize()
+        enc_ms = ev0.elapsed_time(ev1) / 5
+        payload = sum(int(np.maximum(rb.cols[k], 0).sum()) for k in ("path_len", "data_len", "elem_len",
+                                                                    "acl_scheme_len", "acl_id_len"))
+        alg = dr.nbytes() - int(rb.arena.size) - 32 + payload + enc_n + 9 * rb.n
+        line["encode"] = {
+            "packets": rb.n, "frame_bytes": enc_n, "ms": enc_ms, "packets_per_s": rb.n / (enc_ms * 1e-3),
+            "frames_GBps": enc_n / (enc_ms * 1e-3) / 1e9,
+            "roofline": {"bound": "hbm", "achieved": alg / (enc_ms * 1e-3) / 1e9, "peak": measured_peak()[0], "unit": "GB/s",
+                         "frac": alg / (enc_ms * 1e-3) / 1e9 / measured_peak()[0],
+                         "algorithmic_bytes": "descriptor columns + payload bytes read + frames, frame_off and status written"},
+            "launches_per_call": (ctx.kernel_launches - l0) / 5,
+            "sample": "requests of the first %d sessions, re-encoded from their decoded columns (zkb_encode_dev)" % ns_enc,
+        }
+        del dr, out
+
     # ---- CPU baseline beside it (rank 0, N=1 only) ----
     if rank == 0 and world == 1 and not args.no_cpu:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -456,6 +493,7 @@ def main():
     ap.add_argument("--gb", type=float, default=10.0, help="wire bytes per GPU, in GB")
     ap.add_argument("--seed", type=int, default=20240607)
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-encode", action="store_true", help="skip the encode leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = env_int("RANK", 0)
