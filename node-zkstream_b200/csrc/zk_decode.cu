@@ -1408,6 +1408,12 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane)
 }
 
 #define ZK_SPIN_LIMIT (1u << 26)
+#ifndef ZK_SLEEP_MIN
+#define ZK_SLEEP_MIN 128u   /* ns; the look-back's poll interval doubles from here ... */
+#endif
+#ifndef ZK_SLEEP_MAX
+#define ZK_SLEEP_MAX 1024u  /* ... to here */
+#endif
 
 /* Build with -DZK_PROFILE_PHASES to accumulate, per chunk, the SM cycles a decode warp spends
  * in each phase (ticket, staging wait, frame loop, counts, look-back, emission) into
@@ -1709,7 +1715,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 		 * j-32-l, j-64-l, j-96-l with four independent loads (one round trip).  It can finish
 		 * as soon as the nearest full prefix has no unpublished chunk in front of it. */
 		int64_t j = (int64_t)chunk - 1;
-		uint32_t spins = 0, ns_sleep = 128;
+		uint32_t spins = 0, ns_sleep = ZK_SLEEP_MIN;
 		for (;;) {
 			uint4 d[4];
 #pragma unroll
@@ -1741,7 +1747,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 				for (;;) {
 					if (++spins > ZK_SPIN_LIMIT) { gave_up = true; break; }
 					__nanosleep(ns_sleep);
-					if (ns_sleep < 1024) ns_sleep <<= 1;
+					if (ns_sleep < ZK_SLEEP_MAX) ns_sleep <<= 1;
 					if (ld_state(a.lb + hole_idx) != ZK_LB_EMPTY) break;
 				}
 				if (gave_up) {
