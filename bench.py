@@ -76,8 +76,10 @@ def pcie_roofline(h2d_gbps_per_gpu):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe).
+    The sampler is started ahead of time (the process needs ~100 ms to come up) and polls every
+    20 ms; stop(t0, t1) keeps the samples whose timestamps fall inside the timed window."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -92,11 +94,13 @@ class ClockSampler:
             os.close(fd)
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+                 "-lms", "20"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """t0, t1: datetime.now() taken right before / after the timed region (None = keep all)."""
+        import datetime
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.proc is None:
             return out
@@ -105,7 +109,7 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, reasons = [], set()
+        rows = []
         try:
             with open(self.path) as f:
                 for line in f:
@@ -113,19 +117,29 @@ class ClockSampler:
                     if len(p) < 9:
                         continue
                     try:
-                        sm.append(float(p[1]))
-                        out["sm_max_mhz"] = float(p[2])
+                        ts = datetime.datetime.strptime(p[0], "%Y/%m/%d %H:%M:%S.%f")
+                        rows.append((ts, float(p[1]), float(p[2]), [v.lower().startswith("active") for v in p[5:9]]))
                     except ValueError:
                         continue
-                    for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
-                                        "sw_power_cap"), p[5:9]):
-                        if v.lower().startswith("active"):
-                            reasons.add(name)
             os.unlink(self.path)
         except Exception:
             pass
+        inside = [r for r in rows if t0 is not None and t0 <= r[0] <= t1]
+        if inside:
+            out["window"] = "timed region"
+        else:
+            # nothing landed inside a very short window: the samples around it are the same load
+            inside = [r for r in rows if t0 is None or abs((r[0] - t0).total_seconds()) < 1.0 or
+                      abs((r[0] - t1).total_seconds()) < 1.0]
+            out["window"] = "within 1 s of the timed region"
+        sm = sorted(r[1] for r in inside)
+        reasons = set()
+        for r in inside:
+            out["sm_max_mhz"] = r[2]
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3]):
+                if v:
+                    reasons.add(name)
         if sm:
-            sm.sort()
             out["sm_mhz"] = sm[len(sm) // 2]
             out["samples"] = len(sm)
         out["reasons"] = sorted(reasons)
@@ -303,18 +317,23 @@ def run_ours(args, rank, local_rank, world):
                             slow_frames=counts.pop("slow_" + name, None))
     frames_per_step = counts["req"]["frames"] + counts["rsp"]["frames"]
 
+    import datetime
     sampler = ClockSampler(gpu_index_for(local_rank))
+    sampler.start()
+    for _ in range(2):          # keeps the GPU under the same load while the sampler comes up
+        step_dev()
     phases = []
     launches0 = ctx.kernel_launches
     barrier()
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall0 = datetime.datetime.now()
     e0.record(ext)
     for _ in range(args.steps):
         step_dev(phases)
     e1.record(ext)
     barrier()
-    clocks = sampler.stop()
+    wall1 = datetime.datetime.now()
+    clocks = sampler.stop(wall0, wall1)
     launches = ctx.kernel_launches - launches0
     ms = e0.elapsed_time(e1)
     if use_dist:
