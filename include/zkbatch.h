@@ -282,6 +282,14 @@ uint64_t zkb_kernel_launches(const zkb_ctx *ctx);
 /* Number of extra splitter iterations (entry-point guesses that had to be corrected) this
  * context has needed so far; 0 on ordinary traffic.  Diagnostic only. */
 uint64_t zkb_split_fixups(const zkb_ctx *ctx);
+/* Decode passes this context has had to run twice.  The splitter predicts from the frame
+ * headers how many side-table rows every chunk will produce, so that the decode kernel can
+ * place rows without waiting for the chunks before it; a frame that does not keep what its
+ * header promises (malformed body, handshake deeper than the splitter can see) is noticed by
+ * the kernel and the pass is repeated with ordered look-back placement — same result, roughly
+ * one extra decode kernel.  0 on well-formed traffic.  ZKBATCH_NO_PREDICT=1 in the environment
+ * (read at zkb_ctx_create) turns the prediction off.  Diagnostic only. */
+uint64_t zkb_row_mispredicts(const zkb_ctx *ctx);
 /* Frames of the last decode call that were not well-formed (or reached past the staged
  * tile) and therefore went through the exact, slower reader.  Diagnostic only. */
 uint64_t zkb_last_slow_frames(const zkb_ctx *ctx);

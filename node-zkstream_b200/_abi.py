@@ -80,6 +80,7 @@ SYMBOLS = [
     ("zkb_last_error", C.c_char_p, [P]),
     ("zkb_kernel_launches", C.c_uint64, [P]),
     ("zkb_split_fixups", C.c_uint64, [P]),
+    ("zkb_row_mispredicts", C.c_uint64, [P]),
     ("zkb_last_slow_frames", C.c_uint64, [P]),
     ("zkb_ctx_set_timing", C.c_int, [P, C.c_int]),
     ("zkb_last_phase_ms", C.c_int, [P, C.POINTER(C.c_float * 3)]),

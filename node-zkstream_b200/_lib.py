@@ -128,6 +128,11 @@ class Context:
         return int(self._lib.zkb_split_fixups(self._h))
 
     @property
+    def row_mispredicts(self):
+        """Decode passes repeated with look-back placement (see zkb_row_mispredicts)."""
+        return int(self._lib.zkb_row_mispredicts(self._h))
+
+    @property
     def last_slow_frames(self):
         return int(self._lib.zkb_last_slow_frames(self._h))
 

@@ -53,6 +53,7 @@ ZKB_EXPORT int zkb_ctx_create(int device_id, zkb_ctx **out)
 	zkb_ctx *ctx = new (std::nothrow) zkb_ctx();
 	if (!ctx) return ZKB_ENOMEM;
 	memset(ctx, 0, sizeof (*ctx));
+	{ const char *np = getenv("ZKBATCH_NO_PREDICT"); ctx->no_predict = np && np[0] == '1'; }
 	ctx->device = device_id;
 	strcpy(ctx->err, "");
 	cudaDeviceProp prop;
@@ -99,6 +100,7 @@ ZKB_EXPORT void zkb_ctx_destroy(zkb_ctx *ctx)
 
 ZKB_EXPORT const char *zkb_last_error(const zkb_ctx *ctx) { return ctx ? ctx->err : "no context"; }
 ZKB_EXPORT uint64_t zkb_kernel_launches(const zkb_ctx *ctx) { return ctx ? ctx->launches : 0; }
+ZKB_EXPORT uint64_t zkb_row_mispredicts(const zkb_ctx *ctx) { return ctx ? ctx->mispredicts : 0; }
 ZKB_EXPORT uint64_t zkb_split_fixups(const zkb_ctx *ctx) { return ctx ? ctx->split_fixups : 0; }
 ZKB_EXPORT uint64_t zkb_last_slow_frames(const zkb_ctx *ctx) { return ctx ? ctx->slow_frames : 0; }
 #ifdef ZK_PROFILE_PHASES
@@ -268,7 +270,7 @@ ZKB_EXPORT int zkb_decode_host(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbyt
 
 	/* ---- phase A gives the exact frame count, so FRAMES columns are sized exactly ---- */
 	uint64_t n_frames = 0;
-	if ((rc = zk_split_device(ctx, d_bytes, nbytes, &dsess, &n_frames))) return rc;
+	if ((rc = zk_split_device(ctx, d_bytes, nbytes, &dsess, have_xid ? &dxid : NULL, &n_frames))) return rc;
 
 	/* side tables: a Stat needs >= 88 input bytes, a buffer row >= 4; start from what typical
 	 * traffic needs and re-run phase B with the exact counts if that was too small */
@@ -497,7 +499,7 @@ static int replay_decode_dir(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbyt
 	int rc;
 	uint64_t n_frames = 0;
 	const uint32_t nsess = ds->nsessions;
-	if ((rc = zk_split_device(ctx, d_bytes, nbytes, ds, &n_frames))) return rc;
+	if ((rc = zk_split_device(ctx, d_bytes, nbytes, ds, dx, &n_frames))) return rc;
 	uint64_t cs = n_frames < nbytes / 88 + 1 ? n_frames : nbytes / 88 + 1;
 	uint64_t cb = n_frames * 2 + nbytes / 64 + 16;
 	if (cb > nbytes / 4 + 1) cb = nbytes / 4 + 1;

@@ -123,6 +123,11 @@ struct SplitArgs {
 	const uint64_t *sess_off;
 	uint32_t        nsess;
 	const uint8_t  *sess_flags;
+	const uint32_t *sess_hs;
+	const int32_t  *xt_base;     /* xid table of the batch (responses), NULL = none */
+	const uint32_t *xt_count;
+	const uint64_t *xt_off;
+	const int8_t   *xt_ops;
 	uint32_t        glog2;
 	uint32_t        n_gran;
 	/* two walk results per granule ([version * n_gran + g]): version 0 is the walk from the
@@ -131,6 +136,8 @@ struct SplitArgs {
 	uint64_t       *g_assumed;   /* entry position the walk assumed */
 	uint64_t       *g_out;       /* exit: next frame start >= granule end | NONE | INHERIT */
 	uint32_t       *g_cnt;       /* frames starting in the granule */
+	uint4          *g_rows;      /* [version][g] { stat, buf, acl } rows those frames should produce (predict_rows) */
+	uint4          *g_rbase;     /* [n_gran + 1] exclusive prefix of the selected g_rows; [n_gran] = totals */
 	uint8_t        *g_sel;
 	uint64_t       *g_carry;     /* scan result: exit of the nearest predecessor that had one */
 	uint32_t       *g_base;      /* exclusive prefix of g_cnt */
@@ -318,13 +325,170 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 	return ZK_NONE;
 }
 
-/* The loop of ZKDecodeStream._transform (zk-streams.js:47-64) restricted to the frames
- * that start before `ge`: counts them and returns where the chain stands afterwards
- * (ZK_NONE once the session's chain has ended: stream exhausted, frame incomplete, or
- * BAD_LENGTH).  The decode kernel repeats this walk on the staged bytes to place frames. */
-__device__ uint64_t walk_chain(const SplitArgs &a, uint64_t pos, uint64_t send, uint64_t ge, uint32_t &count,
-    uint64_t gs, uint16_t *row, uint32_t &last_sub)
+/* ---- side-table rows a frame should produce ------------------------------------------
+ * The walk has every frame header in hand, and for a well-formed frame the header (plus a
+ * vector count right behind it) settles how many STAT / BUF / ACL rows the frame owns.  The
+ * walk adds these up per granule, the scan turns them into each decode chunk's first row, and
+ * k_decode<true> places its rows there without waiting for its predecessors; it compares what
+ * it really found with the prediction, and a single mismatch (a malformed frame, a handshake
+ * depth the walk cannot know) makes the host repeat the pass with the look-back.  So this is a
+ * guess that costs time when wrong, never a wrong answer. */
+struct RowCnt { uint32_t st, bf, ac; };
+
+__device__ __forceinline__ int special_xid_op(int32_t xid)
 {
+	return xid == ZKB_XID_NOTIFICATION ? ZKB_OP_NOTIFICATION : xid == ZKB_XID_PING ? ZKB_OP_PING :
+	    xid == ZKB_XID_AUTH ? ZKB_OP_AUTH : xid == ZKB_XID_SET_WATCHES ? ZKB_OP_SET_WATCHES : ZKB_OP_NONE;
+}
+
+/* The first 24 bytes at a frame start as six big-endian words: length prefix, then payload
+ * words 0..4 (request: xid, type, path length; reply: xid, zxid, zxid, err, vector count).
+ * Loaded together, one round trip; bytes past the end of the batch read as zero. */
+struct Hdr { uint32_t len, w1, w2, w3, w4, w5; };   /* w1 = xid, w2 = request type, w3 = request path length, w4 = reply err, w5 = vector count */
+
+__device__ __forceinline__ Hdr load_hdr(const uint8_t *bytes, uint64_t pos, uint64_t padend, bool server)
+{
+	Hdr h;
+	const uint64_t base = pos & ~3ull;
+	const uint32_t sh = (uint32_t)(pos & 3) * 8;
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(bytes + base);
+	uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0, x5 = 0, x6 = 0;
+	if (base + 28 <= padend) {
+		/* a request is settled by its first 16 bytes (CREATE follows its buffers from there) */
+		x0 = __ldg(p); x1 = __ldg(p + 1); x2 = __ldg(p + 2); x3 = __ldg(p + 3); x4 = __ldg(p + 4);
+		if (!server) { x5 = __ldg(p + 5); x6 = __ldg(p + 6); }
+	} else {
+		if (base + 4 <= padend) x0 = __ldg(p);
+		if (base + 8 <= padend) x1 = __ldg(p + 1);
+		if (base + 12 <= padend) x2 = __ldg(p + 2);
+		if (base + 16 <= padend) x3 = __ldg(p + 3);
+		if (base + 20 <= padend) x4 = __ldg(p + 4);
+		if (base + 24 <= padend) x5 = __ldg(p + 5);
+	}
+	h.len = bswap32(__funnelshift_r(x0, x1, sh));
+	h.w1 = bswap32(__funnelshift_r(x1, x2, sh));
+	h.w2 = bswap32(__funnelshift_r(x2, x3, sh));
+	h.w3 = bswap32(__funnelshift_r(x3, x4, sh));
+	h.w4 = bswap32(__funnelshift_r(x4, x5, sh));
+	h.w5 = bswap32(__funnelshift_r(x5, x6, sh));
+	return h;
+}
+
+/* per-session constants of the prediction */
+struct SessCtx {
+	bool     server;
+	uint32_t hs;
+	int64_t  xbase;
+	int64_t  xcount;
+	const int8_t *xops;     /* ops of this session, NULL = no table */
+};
+
+__device__ __forceinline__ SessCtx sess_ctx(const SplitArgs &a, uint32_t s)
+{
+	SessCtx c;
+	c.server = a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER);
+	c.hs = a.sess_hs ? __ldg(a.sess_hs + s) : 1u;
+	c.xops = NULL; c.xbase = 0; c.xcount = 0;
+	if (a.xt_ops && !c.server) {
+		c.xbase = (int64_t)__ldg(a.xt_base + s);
+		c.xcount = (int64_t)__ldg(a.xt_count + s);
+		c.xops = a.xt_ops + __ldg(a.xt_off + s);
+	}
+	return c;
+}
+
+__device__ void predict_rows(const SplitArgs &a, uint64_t pos, const Hdr &h, const SessCtx &sc, bool handshake,
+    RowCnt &r)
+{
+	const uint64_t pay = pos + 4;
+	const uint32_t L = h.len;
+	if (handshake) {
+		/* readConnectRequest / readConnectResponse (zk-buffer.js:22-30, 41-48): one buffer, passwd */
+		if (L >= (sc.server ? 28u : 20u)) r.bf += 1;
+		return;
+	}
+	if (sc.server) {                                /* readRequest zk-buffer.js:58-95 */
+		if (L < 8) return;
+		switch ((int32_t)h.w2) {
+		case ZKB_OP_GET_CHILDREN: case ZKB_OP_GET_CHILDREN2: case ZKB_OP_GET_DATA: case ZKB_OP_EXISTS:
+		case ZKB_OP_DELETE: case ZKB_OP_GET_ACL: case ZKB_OP_SYNC:
+			r.bf += 1; return;
+		case ZKB_OP_SET_DATA:
+			r.bf += 2; return;
+		case ZKB_OP_CREATE: {
+			if (L < 12) return;
+			const int32_t pl = (int32_t)h.w3;
+			const uint64_t c1 = 12ull + (pl > 0 ? (uint32_t)pl : 0u);
+			if (c1 + 4 > L) return;
+			const int32_t dl = (int32_t)g_be32(a.bytes, pay + c1);
+			const uint64_t c2 = c1 + 4 + (dl > 0 ? (uint32_t)dl : 0u);
+			if (c2 + 4 > L) return;
+			const int32_t n = (int32_t)g_be32(a.bytes, pay + c2);
+			const uint32_t k = n > 0 ? (uint32_t)n : 0u;
+			r.bf += 2 + 2 * k; r.ac += k;
+			return;
+		}
+		case ZKB_OP_SET_WATCHES: {
+			uint64_t cur = 16;
+			uint32_t nb = 0;
+			for (int v = 0; v < 3; ++v) {
+				if (cur + 4 > L) return;
+				const int32_t n = (int32_t)g_be32(a.bytes, pay + cur);
+				cur += 4;
+				for (int32_t i = 0; i < n; ++i) {
+					if (cur + 4 > L) return;
+					const int32_t l = (int32_t)g_be32(a.bytes, pay + cur);
+					cur += 4ull + (l > 0 ? (uint32_t)l : 0u);
+					nb++;
+				}
+			}
+			r.bf += nb;
+			return;
+		}
+		default: return;                            /* 'Unsupported opcode': no packet, no rows */
+		}
+	}
+	/* readResponse zk-buffer.js:281-331 */
+	if (L < 16) return;
+	const int32_t xid = (int32_t)h.w1;
+	int op = special_xid_op(xid);
+	if (op == ZKB_OP_NONE && sc.xops) {
+		const int64_t idx = (int64_t)xid - sc.xbase;
+		if (idx >= 0 && idx < sc.xcount) op = __ldg(sc.xops + idx);
+	}
+	if (op == ZKB_OP_NONE) return;
+	if (h.w4 != 0) return;                          /* only 'OK' replies have a body */
+	switch (op) {
+	case ZKB_OP_GET_CHILDREN: case ZKB_OP_GET_CHILDREN2: case ZKB_OP_GET_ACL: {
+		if (L < 20) return;
+		const int32_t n = (int32_t)h.w5;
+		const uint32_t k = n > 0 ? (uint32_t)n : 0u;
+		if (op == ZKB_OP_GET_ACL) { r.bf += 2 * k; r.ac += k; r.st += 1; }
+		else { r.bf += k; if (op == ZKB_OP_GET_CHILDREN2) r.st += 1; }
+		return;
+	}
+	case ZKB_OP_CREATE: case ZKB_OP_NOTIFICATION: r.bf += 1; return;
+	case ZKB_OP_GET_DATA: r.bf += 1; r.st += 1; return;
+	case ZKB_OP_EXISTS: case ZKB_OP_SET_DATA: r.st += 1; return;
+	default: return;
+	}
+}
+
+/* The loop of ZKDecodeStream._transform (zk-streams.js:47-64) restricted to the frames
+ * that start before `ge`: counts them (and the rows they should produce) and returns where
+ * the chain stands afterwards (ZK_NONE once the session's chain has ended: stream exhausted,
+ * frame incomplete, or BAD_LENGTH).  `fidx` is the index within session `s` of the frame at
+ * `pos`, or ZK_FIDX_UNKNOWN when the walk entered the session somewhere in the middle.  The
+ * header of the next frame is requested before the current frame's rows are worked out, so
+ * the table lookups of the prediction overlap that round trip.  The decode kernel repeats
+ * this walk on the staged bytes to place frames. */
+#define ZK_FIDX_UNKNOWN 0xFFFFFFFFu
+__device__ uint64_t walk_chain(const SplitArgs &a, uint64_t pos, uint64_t send, uint64_t ge, uint32_t &count,
+    uint64_t gs, uint16_t *row, uint32_t &last_sub, RowCnt &rows, uint32_t s, uint32_t fidx)
+{
+	const SessCtx sc = sess_ctx(a, s);
+	const uint64_t padend = (a.nbytes + 15) & ~15ull;
+	Hdr h = load_hdr(a.bytes, pos < ge ? pos : 0, padend, sc.server);
 	for (;;) {
 		if (pos < ge) {
 			/* positions only grow, so each sub-range is recorded at most once */
@@ -335,18 +499,27 @@ __device__ uint64_t walk_chain(const SplitArgs &a, uint64_t pos, uint64_t send, 
 		if (pos >= ge) return pos;
 		const uint64_t rem = send - pos;
 		if (rem < 4) return ZK_NONE;                        /* zd_used < 4 */
-		const int32_t len = (int32_t)g_be32(a.bytes, pos);
+		const int32_t len = (int32_t)h.len;
 		if (!len_ok(len)) return ZK_NONE;                   /* :49-53 BAD_LENGTH */
 		if (rem < 4 + (uint64_t)len) return ZK_NONE;        /* frame not complete yet */
 		count++;
-		pos += 4 + (uint64_t)len;
+		const uint64_t next = pos + 4 + (uint64_t)len;
+		Hdr hn;
+		if (next < ge) hn = load_hdr(a.bytes, next, padend, sc.server);
+		/* a walk that entered mid-session is past the handshake unless every frame is one */
+#ifndef ZK_EXP_NO_ROWPRED
+		predict_rows(a, pos, h, sc, fidx == ZK_FIDX_UNKNOWN ? sc.hs == 0xFFFFFFFFu : fidx < sc.hs, rows);
+#endif
+		if (fidx != ZK_FIDX_UNKNOWN) fidx++;
+		pos = next;
+		h = hn;
 	}
 }
 
 /* One granule's walk: the chain that enters at `assumed` (if that lies inside the granule)
  * and then every session that starts inside it.  Fills the granule's row of sub-range
  * entries; `out` is where the last chain stands afterwards (ZK_INHERIT if nothing was walked). */
-struct GranWalk { uint64_t out; uint32_t count; uint32_t open_local; };
+struct GranWalk { uint64_t out; uint32_t count; uint32_t open_local; RowCnt rows; };
 
 __device__ GranWalk walk_granule(const SplitArgs &a, uint32_t g, uint32_t sf, uint64_t assumed, uint16_t *row)
 {
@@ -356,20 +529,20 @@ __device__ GranWalk walk_granule(const SplitArgs &a, uint32_t g, uint32_t sf, ui
 	const uint32_t subs = 1u << (a.glog2 - 8);
 	for (uint32_t i = 0; i < subs; i += 8)
 		*reinterpret_cast<uint4 *>(row + i) = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-	GranWalk w; w.count = 0; w.open_local = 0;
+	GranWalk w; w.count = 0; w.open_local = 0; w.rows.st = w.rows.bf = w.rows.ac = 0;
 	uint64_t pos = ZK_NONE;
 	bool touched = false;
 	uint32_t last_sub = 0xFFFFFFFFu;
 	if (__ldg(a.sess_off + sf) != gs && assumed >= gs && assumed < ge) {   /* inside session sf-1 */
 		touched = true;
-		pos = walk_chain(a, assumed, __ldg(a.sess_off + sf), ge, w.count, gs, row, last_sub);
+		pos = walk_chain(a, assumed, __ldg(a.sess_off + sf), ge, w.count, gs, row, last_sub, w.rows, sf - 1, ZK_FIDX_UNKNOWN);
 	}
 	for (uint32_t s = sf; s < a.nsess; ++s) {
 		uint64_t so = __ldg(a.sess_off + s);
 		if (!(so < ge || last)) break;
 		touched = true;
 		w.open_local = w.count;
-		pos = walk_chain(a, so, __ldg(a.sess_off + s + 1), ge, w.count, gs, row, last_sub);
+		pos = walk_chain(a, so, __ldg(a.sess_off + s + 1), ge, w.count, gs, row, last_sub, w.rows, s, 0);
 	}
 	w.out = touched ? pos : ZK_INHERIT;
 	return w;
@@ -429,6 +602,7 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		a.g_assumed[g] = assumed; a.g_out[g] = w.out; a.g_cnt[g] = w.count; a.g_openlocal[g] = w.open_local;
 		a.g_assumed[a.n_gran + g] = assumed; a.g_out[a.n_gran + g] = w.out; a.g_cnt[a.n_gran + g] = w.count;
 		a.g_openlocal[a.n_gran + g] = w.open_local;
+		a.g_rows[g] = a.g_rows[a.n_gran + g] = make_uint4(w.rows.st, w.rows.bf, w.rows.ac, 0);
 		a.g_sel[g] = 0;
 		a.g_sf[g] = sf;
 		return;
@@ -450,6 +624,7 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 		const GranWalk w = walk_granule(a, g, a.g_sf[g], carry, a.g_sub + ((size_t)a.n_gran + g) * subs);
 		a.g_assumed[a.n_gran + g] = carry; a.g_out[a.n_gran + g] = w.out; a.g_cnt[a.n_gran + g] = w.count;
 		a.g_openlocal[a.n_gran + g] = w.open_local;
+		a.g_rows[a.n_gran + g] = make_uint4(w.rows.st, w.rows.bf, w.rows.ac, 0);
 		a.g_sel[g] = 1;
 		if (w.out != ZK_INHERIT) carry = w.out;
 	}
@@ -474,6 +649,7 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 			const GranWalk w = walk_granule(a, h, a.g_sf[h], nc, a.g_sub + ((size_t)a.n_gran + h) * subs);
 			a.g_assumed[a.n_gran + h] = nc; a.g_out[a.n_gran + h] = w.out; a.g_cnt[a.n_gran + h] = w.count;
 			a.g_openlocal[a.n_gran + h] = w.open_local;
+			a.g_rows[a.n_gran + h] = make_uint4(w.rows.st, w.rows.bf, w.rows.ac, 0);
 			a.g_sel[h] = 1;
 			hout = w.out;
 			changed = true;
@@ -488,7 +664,7 @@ __global__ void __launch_bounds__(128) k_split(SplitArgs a)
 
 /* ---- scan over granules: value = (last exit that is not INHERIT, sum of counts) ------ */
 
-struct ScanVal { uint64_t v; uint32_t c; uint32_t src; uint32_t ssrc; uint32_t pad; };
+struct ScanVal { uint64_t v; uint32_t c; uint32_t src; uint32_t ssrc; uint32_t r0, r1, r2; };
 
 __device__ __forceinline__ ScanVal sv_comb(ScanVal l, ScanVal r)
 {
@@ -497,7 +673,7 @@ __device__ __forceinline__ ScanVal sv_comb(ScanVal l, ScanVal r)
 	o.src = (r.v != ZK_INHERIT) ? r.src : l.src;
 	o.ssrc = r.ssrc ? r.ssrc : l.ssrc;
 	o.c = l.c + r.c;
-	o.pad = 0;
+	o.r0 = l.r0 + r.r0; o.r1 = l.r1 + r.r1; o.r2 = l.r2 + r.r2;
 	return o;
 }
 __device__ __forceinline__ ScanVal sv_shfl_up(ScanVal x, int d)
@@ -507,7 +683,9 @@ __device__ __forceinline__ ScanVal sv_shfl_up(ScanVal x, int d)
 	o.c = __shfl_up_sync(0xffffffffu, x.c, d);
 	o.src = __shfl_up_sync(0xffffffffu, x.src, d);
 	o.ssrc = __shfl_up_sync(0xffffffffu, x.ssrc, d);
-	o.pad = 0;
+	o.r0 = __shfl_up_sync(0xffffffffu, x.r0, d);
+	o.r1 = __shfl_up_sync(0xffffffffu, x.r1, d);
+	o.r2 = __shfl_up_sync(0xffffffffu, x.r2, d);
 	return o;
 }
 
@@ -523,7 +701,7 @@ __device__ ScanVal block_scan_incl(ScanVal x, ScanVal *total, ScanVal *s_w /* [3
 	}
 	if (lane == 31) s_w[wid] = x;
 	__syncthreads();
-	ScanVal pre; pre.v = ZK_INHERIT; pre.c = 0; pre.src = 0; pre.ssrc = 0; pre.pad = 0;
+	ScanVal pre; pre.v = ZK_INHERIT; pre.c = 0; pre.src = 0; pre.ssrc = 0; pre.r0 = pre.r1 = pre.r2 = 0;
 	ScanVal tot = pre;
 	const int nw = blockDim.x >> 5;
 	for (int w = 0; w < nw; ++w) {
@@ -539,10 +717,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 {
 	__shared__ ScanVal s_w[32];
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
-	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.pad = 0;
+	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.r0 = x.r1 = x.r2 = 0;
 	if (g < a.n_gran) {
 		const size_t i = (size_t)a.g_sel[g] * a.n_gran + g;
 		x.v = a.g_out[i]; x.c = a.g_cnt[i]; x.src = g + 1;
+		{ const uint4 rw = a.g_rows[i]; x.r0 = rw.x; x.r1 = rw.y; x.r2 = rw.z; }
 		const uint32_t sf = a.g_sf[g];
 		const uint64_t gend = (g == a.n_gran - 1) ? a.nbytes + 1 : ((uint64_t)(g + 1) << a.glog2);
 		x.ssrc = (sf < a.nsess && __ldg(a.sess_off + sf) < gend) ? g + 1 : 0;
@@ -556,10 +735,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint32_t nblk)
 {
 	__shared__ ScanVal s_w[32];
-	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.src = 0; carry.ssrc = 0; carry.pad = 0;
+	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.src = 0; carry.ssrc = 0; carry.r0 = carry.r1 = carry.r2 = 0;
 	for (uint32_t b0 = 0; b0 < nblk; b0 += SCAN_THREADS) {
 		uint32_t i = b0 + threadIdx.x;
-		ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.pad = 0;
+		ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.r0 = x.r1 = x.r2 = 0;
 		if (i < nblk) x = blk[i];
 		ScanVal tot;
 		ScanVal inc = block_scan_incl(x, &tot, s_w);
@@ -569,7 +748,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint
 		if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
 		__syncthreads();
 		ScanVal ex;
-		if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; ex.ssrc = 0; ex.pad = 0; }
+		if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; ex.ssrc = 0; ex.r0 = ex.r1 = ex.r2 = 0; }
 		else if ((threadIdx.x & 31) == 0) ex = s_last[(threadIdx.x >> 5) - 1];
 		else ex = prev;
 		if (i < nblk) blk[i] = sv_comb(carry, ex);
@@ -583,10 +762,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	__shared__ ScanVal s_w[32];
 	__shared__ ScanVal s_last[32];
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
-	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.pad = 0;
+	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.r0 = x.r1 = x.r2 = 0;
 	if (g < a.n_gran) {
 		const size_t i = (size_t)a.g_sel[g] * a.n_gran + g;
 		x.v = a.g_out[i]; x.c = a.g_cnt[i]; x.src = g + 1;
+		{ const uint4 rw = a.g_rows[i]; x.r0 = rw.x; x.r1 = rw.y; x.r2 = rw.z; }
 		const uint32_t sf = a.g_sf[g];
 		const uint64_t gend = (g == a.n_gran - 1) ? a.nbytes + 1 : ((uint64_t)(g + 1) << a.glog2);
 		x.ssrc = (sf < a.nsess && __ldg(a.sess_off + sf) < gend) ? g + 1 : 0;
@@ -597,7 +777,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
 	__syncthreads();
 	ScanVal ex;
-	if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; ex.ssrc = 0; ex.pad = 0; }
+	if (threadIdx.x == 0) { ex.v = ZK_INHERIT; ex.c = 0; ex.src = 0; ex.ssrc = 0; ex.r0 = ex.r1 = ex.r2 = 0; }
 	else if ((threadIdx.x & 31) == 0) ex = s_last[(threadIdx.x >> 5) - 1];
 	else ex = prev;
 	ex = sv_comb(blk[blockIdx.x], ex);
@@ -607,6 +787,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	uint64_t carry = (ex.v == ZK_INHERIT) ? ZK_NONE : ex.v;
 	a.g_carry[g] = carry;
 	a.g_base[g] = ex.c;
+	a.g_rbase[g] = make_uint4(ex.r0, ex.r1, ex.r2, 0);
+	if (g == a.n_gran - 1) a.g_rbase[a.n_gran] = make_uint4(ex.r0 + x.r0, ex.r1 + x.r1, ex.r2 + x.r2, 0);
 	a.g_src[g] = (ex.v == ZK_INHERIT) ? 0u : ex.src;
 	a.g_ssrc[g] = ex.ssrc;
 	/* a walk is consistent with the carry iff both name the same in-granule position, or
@@ -670,6 +852,7 @@ struct DecArgs {
 	const uint32_t *g_openlocal;  /* [version][g] */
 	const uint16_t *g_sub;        /* [version][g][granule/256] chain entry per 256-byte sub-range */
 	const uint8_t  *g_sel;
+	const uint4    *g_rbase;      /* [n_gran + 1] predicted first { stat, buf, acl } row per granule */
 	uint32_t        glog2;
 	uint32_t        n_gran;
 	uint32_t        n_chunks;
@@ -1431,6 +1614,7 @@ __device__ unsigned long long zk_hist[3][64];
 
 /* Everything one warp does for one 8 KiB chunk.  `phase` is the parity of the warp's
  * mbarrier for this use (it flips every chunk). */
+template <bool PRED>
 __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
     const uint32_t chunk, const uint32_t lane, const long long zk_t0)
 {
@@ -1462,6 +1646,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	const uint32_t g0 = chunk << gsh, g1 = (chunk + 1) << gsh;
 	const uint32_t f0 = a.g_base[g0];
 	const uint32_t f1 = (g1 < a.n_gran) ? a.g_base[g1] : (uint32_t)a.n_frames;
+
 	const uint32_t nfr = f1 - f0;
 	const bool last = (chunk == a.n_chunks - 1);
 	const uint64_t ce = last ? a.nbytes : cs + ZK_CHUNK;
@@ -1709,7 +1894,17 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	 * the chunk's own totals (AGG), later its inclusive prefix (PFX). ---- */
 	ZK_T(5);
 	uint32_t e0 = 0, e1 = 0, e2 = 0;
-	if (chunk > 0) {
+	if (PRED) {
+		/* The splitter predicted this chunk's rows (predict_rows): they start at rb0 if every
+		 * chunk really has what was predicted for it.  One that does not raises the flag; the
+		 * host then repeats the pass with the look-back, and this pass's rows do not matter. */
+		const uint4 rb0 = a.g_rbase[g0], rb1 = a.g_rbase[g1 < a.n_gran ? g1 : a.n_gran];
+		e0 = rb0.x; e1 = rb0.y; e2 = rb0.z;
+		if (ts != rb1.x - rb0.x || tb != rb1.y - rb0.y || ta != rb1.z - rb0.z) {
+			if (lane == 0) atomicOr(&a.ctrl->error, ZK_DERR_MISPREDICT);
+			return;
+		}
+	} else if (chunk > 0) {
 		if (lane == 0) st_desc(a.lb + chunk, make_uint4(ZK_LB_AGG, ts, tb, ta));
 		/* Each round looks at the 128 chunks before position j: lane l reads chunks j-l,
 		 * j-32-l, j-64-l, j-96-l with four independent loads (one round trip).  It can finish
@@ -1762,7 +1957,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 		}
 	}
 	if (lane == 0) {
-		st_desc(a.lb + chunk, make_uint4(ZK_LB_PFX, e0 + ts, e1 + tb, e2 + ta));
+		if (!PRED) st_desc(a.lb + chunk, make_uint4(ZK_LB_PFX, e0 + ts, e1 + tb, e2 + ta));
 		if (chunk == a.n_chunks - 1) {
 			a.ctrl->n_stat = (unsigned long long)e0 + ts;
 			a.ctrl->n_buf = (unsigned long long)e1 + tb;
@@ -1887,6 +2082,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 #ifndef ZK_DEC_MINBLOCKS
 #define ZK_DEC_MINBLOCKS 5
 #endif
+template <bool PRED>
 __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(DecArgs a)
 {
 	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
@@ -1903,7 +2099,7 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(
 	if (chunk >= a.n_chunks) return;
 	if (lane == 0) mbar_init(bar, 1);
 	__syncwarp();
-	decode_chunk(a, c, bar, 0, chunk, lane, t0);
+	decode_chunk<PRED>(a, c, bar, 0, chunk, lane, t0);
 }
 
 /* ================================================================================== */
@@ -1949,7 +2145,7 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 }
 
 struct ScratchLayout {
-	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, blk, lb, total;
+	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, lb, total;
 	uint32_t glog2, n_gran, n_chunks, n_blk;
 };
 
@@ -1974,6 +2170,8 @@ static ScratchLayout zk_layout(uint64_t nbytes)
 	L.g_openlocal = o; o += zk_align_up((size_t)L.n_gran * 8, 256);
 	L.g_ssrc = o;    o += zk_align_up((size_t)L.n_gran * 4, 256);
 	L.g_sub = o;     o += zk_align_up((size_t)L.n_gran * 2 * ((size_t)1 << (L.glog2 - 8)) * 2, 256);
+	L.g_rows = o;    o += zk_align_up((size_t)L.n_gran * 2 * 16, 256);
+	L.g_rbase = o;   o += zk_align_up((size_t)(L.n_gran + 1) * 16, 256);
 	L.blk = o;       o += zk_align_up((size_t)(L.n_blk + 1) * sizeof (ScanVal), 256);
 	L.lb = o;        o += zk_align_up((size_t)L.n_chunks * 16, 256);
 	L.total = o;
@@ -2001,12 +2199,14 @@ static int zk_read_ctrl(zkb_ctx *ctx)
 	} while (0)
 
 static int zk_fill_split_args(zkb_ctx *ctx, SplitArgs &sa, const ScratchLayout &L,
-    const uint8_t *d_bytes, uint64_t nbytes, const zkb_sessions *sess)
+    const uint8_t *d_bytes, uint64_t nbytes, const zkb_sessions *sess, const zkb_xidtab *xid)
 {
 	uint8_t *S = (uint8_t *)ctx->d_scratch;
 	memset(&sa, 0, sizeof (sa));
 	sa.bytes = d_bytes; sa.nbytes = nbytes; sa.sess_off = sess->off; sa.nsess = sess->nsessions;
-	sa.sess_flags = sess->flags; sa.glog2 = L.glog2; sa.n_gran = L.n_gran;
+	sa.sess_flags = sess->flags; sa.sess_hs = sess->handshake_frames; sa.glog2 = L.glog2; sa.n_gran = L.n_gran;
+	if (xid && xid->ops) { sa.xt_base = xid->base; sa.xt_count = xid->count; sa.xt_off = xid->off; sa.xt_ops = xid->ops; }
+	sa.g_rows = (uint4 *)(S + L.g_rows); sa.g_rbase = (uint4 *)(S + L.g_rbase);
 	sa.g_assumed = (uint64_t *)(S + L.g_assumed); sa.g_out = (uint64_t *)(S + L.g_out);
 	sa.g_carry = (uint64_t *)(S + L.g_carry); sa.g_cnt = (uint32_t *)(S + L.g_cnt);
 	sa.g_base = (uint32_t *)(S + L.g_base); sa.g_dirty = (uint8_t *)(S + L.g_dirty);
@@ -2019,7 +2219,7 @@ static int zk_fill_split_args(zkb_ctx *ctx, SplitArgs &sa, const ScratchLayout &
 
 /* Phase A: find every frame boundary; on success *n_frames is exact. */
 int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
-    const zkb_sessions *sess, uint64_t *n_frames)
+    const zkb_sessions *sess, const zkb_xidtab *xid, uint64_t *n_frames)
 {
 	int rc;
 	*n_frames = 0;
@@ -2052,7 +2252,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	const ScratchLayout L = zk_layout(nbytes);
 	if ((rc = zk_ensure(ctx, &ctx->d_scratch, &ctx->d_scratch_bytes, L.total + 256, 0))) return rc;
 	SplitArgs sa;
-	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess);
+	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, xid);
 	ScanVal *blk = (ScanVal *)((uint8_t *)ctx->d_scratch + L.blk);
 
 	const uint32_t split_blocks = (L.n_gran + 127) / 128;
@@ -2127,7 +2327,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	const ScratchLayout L = zk_layout(nbytes);
 	uint8_t *S = (uint8_t *)ctx->d_scratch;
 	SplitArgs sa;
-	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess);
+	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, xid);
 	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long) * 9, ctx->stream));
 	/* sess_first_frame[nsess] = n_frames */
 	ZK_CUDA(ctx, cudaMemcpyAsync(out->sess_first_frame + nsess, &ctx->d_ctrl->n_frames, sizeof (uint32_t),
@@ -2146,12 +2346,31 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_chunks = L.n_chunks;
 	da.n_frames = n_frames; da.o = *out;
 	da.lb = (uint4 *)(S + L.lb); da.ctrl = ctx->d_ctrl;
-	ZK_CUDA(ctx, cudaMemsetAsync(da.lb, 0, (size_t)L.n_chunks * 16, ctx->stream));
+	da.g_rbase = sa.g_rbase;
+	const unsigned dec_blocks = (L.n_chunks + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS;
 	ZK_EV(ctx, 4);
-	k_decode<<<(L.n_chunks + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
-	LAUNCH_CHECK(ctx);
+	bool lookback = ctx->no_predict != 0;
+	if (!lookback) {
+		/* first try: every chunk places its rows where the splitter predicted */
+		k_decode<true><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		LAUNCH_CHECK(ctx);
+		if ((rc = zk_read_ctrl(ctx))) return rc;
+		if (ctx->h_ctrl->error == ZK_DERR_MISPREDICT) {
+			/* some frame is not what its header promised: same pass again, rows placed by look-back */
+			ctx->mispredicts++;
+			lookback = true;
+			ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->error, 0, sizeof (unsigned int), ctx->stream));
+			ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long) * 9, ctx->stream));
+		}
+	}
+	if (lookback) {
+		ZK_CUDA(ctx, cudaMemsetAsync(da.lb, 0, (size_t)L.n_chunks * 16, ctx->stream));
+		k_decode<false><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		LAUNCH_CHECK(ctx);
+	}
 	ZK_EV(ctx, 5);
-	if ((rc = zk_read_ctrl(ctx))) return rc;
+	if (lookback && (rc = zk_read_ctrl(ctx))) return rc;
+	if (ctx->timing) ZK_CUDA(ctx, cudaEventSynchronize(ctx->ev[5]));
 	if (ctx->timing) {
 		cudaEventElapsedTime(&ctx->phase_ms[0], ctx->ev[0], ctx->ev[1]);
 		ctx->phase_ms[1] = 0.0f;   /* the frame rows are written by the decode kernel itself */
@@ -2182,7 +2401,7 @@ int zk_decode_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 {
 	uint64_t n_frames = 0;
 	if (!out) return ZKB_EINVAL;
-	int rc = zk_split_device(ctx, d_bytes, nbytes, sess, &n_frames);
+	int rc = zk_split_device(ctx, d_bytes, nbytes, sess, xid, &n_frames);
 	if (rc) return rc;
 	return zk_fields_device(ctx, d_bytes, nbytes, sess, xid, n_frames, out);
 }

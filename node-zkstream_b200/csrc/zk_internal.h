@@ -29,6 +29,7 @@
 #define ZK_DERR_SESSIONS  1u  /* session offsets not monotone / not covering the batch */
 #define ZK_DERR_LOOKBACK  2u  /* look-back spin limit hit (would have been a hang) */
 #define ZK_DERR_COUNT     4u  /* frame count disagreed between split and emit */
+#define ZK_DERR_MISPREDICT 8u /* a chunk's side rows differ from the splitter's prediction: redo with the look-back */
 
 struct zk_ctrl {
 	unsigned int       error;
@@ -49,6 +50,8 @@ struct zkb_ctx {
 	uint64_t      launches;
 	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
 	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
+	int           no_predict;     /* ZKBATCH_NO_PREDICT=1: always place side rows by look-back */
+	uint64_t      mispredicts;    /* decode passes repeated with the look-back because a row prediction failed */
 	unsigned long long prof[8];
 	unsigned long long split_prof[8];
 	unsigned int split_iters[32][2];  /* last split: (n_dirty, n_rewalk) after each scan */
@@ -97,7 +100,7 @@ int zk_ensure(zkb_ctx *ctx, void **p, size_t *have, size_t need, int pinned_host
 int zk_decode_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
     const zkb_sessions *d_sess, const zkb_xidtab *d_xid, zkb_decoded *d_out);
 int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
-    const zkb_sessions *d_sess, uint64_t *n_frames);
+    const zkb_sessions *d_sess, const zkb_xidtab *d_xid, uint64_t *n_frames);
 int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
     const zkb_sessions *d_sess, const zkb_xidtab *d_xid, uint64_t n_frames, zkb_decoded *d_out);
 int zk_xidtab_build_device(zkb_ctx *ctx, const zkb_decoded *d_req, uint32_t nsessions,

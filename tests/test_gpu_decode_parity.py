@@ -328,3 +328,47 @@ def test_maximum_frame_length(ctx, oracle, synth, zk):
     assert int(g.buf_len[1]) == body_len and int(g.dataLength[0]) == body_len
     assert int(g.sess_bad_length_at[1]) == int(g.sess_consumed[1]) and int(g.sess_bad_length_at[0]) == zk._abi.NO_OFFSET
     assert int(g.sess_consumed[2]) == int(c.sess_off[2]) + 4 + len(synth.connect_response(rng))
+
+
+def test_row_prediction_and_its_fallback(ctx, oracle, synth, zk, monkeypatch):
+    """Side rows are placed where the splitter predicted; the kernel checks the prediction and
+    the pass is repeated with the look-back when it fails.  Well-formed traffic must never need
+    the second pass, damaged traffic must get it, and both ways must give the oracle's rows."""
+    pc = synth.native_cfg2(17, 24, 4000)
+    n = pc.nsessions
+    before = ctx.row_mispredicts
+    req = ctx.decode_host(pc.req, pc.req_off, pc.req_flags, None, None)
+    xt = ctx.xidtab_build_host(req, zk.XidTable(np.zeros(n, np.int32), np.full(n, pc.frames, np.uint32)))
+    rsp = ctx.decode_host(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt)
+    c3 = synth.cfg3_tiny(20, 500, seed=8)
+    g3, o3 = both(ctx, oracle, c3)
+    assert g3.diff(o3) == []
+    c4 = synth.cfg4_large(4, payload=200000, children=(2000, 5000))
+    g4, o4 = both(ctx, oracle, c4)
+    assert g4.diff(o4) == []
+    assert ctx.row_mispredicts == before, "well-formed traffic took the fallback"
+    assert req.diff(oracle.decode(pc.req, pc.req_off, pc.req_flags, None, None)) == []
+    assert rsp.diff(oracle.decode(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt)) == []
+    # damaged frames: prediction must fail somewhere, result still exact
+    f = synth.fuzz_corpus(4242, nsessions=200, max_frames=60)
+    g, o = both(ctx, oracle, f)
+    assert g.diff(o) == []
+    assert ctx.row_mispredicts > before
+    # handshake depth the walk cannot see (3 connect frames, the third in a later granule)
+    import random
+    rng = random.Random(1)
+    c = synth.Corpus()
+    filler = synth.frame(synth.connect_response(rng, passwd_len=9000))
+    c.add(filler + filler + synth.frame(synth.connect_response(rng)) + synth.frame(synth.resp_header(-2, 1, 0)), hs=3)
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == [] and g.n_buf == 3
+    # and with the prediction switched off the same columns come out
+    monkeypatch.setenv("ZKBATCH_NO_PREDICT", "1")
+    ctx2 = zk.Context(0)
+    try:
+        d, off, fl, hs = c3.arrays()
+        assert ctx2.decode_host(d, off, fl, hs, c3.xidtable()).diff(o3) == []
+        assert ctx2.decode_host(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt).diff(rsp) == []
+        assert ctx2.row_mispredicts == 0
+    finally:
+        ctx2.close()
