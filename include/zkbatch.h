@@ -286,8 +286,8 @@ uint64_t zkb_split_fixups(const zkb_ctx *ctx);
  * headers how many side-table rows every chunk will produce, so that the decode kernel can
  * place rows without waiting for the chunks before it; a frame that does not keep what its
  * header promises (malformed body, handshake deeper than the splitter can see) is noticed by
- * the kernel and the pass is repeated with ordered look-back placement — same result, roughly
- * one extra decode kernel.  0 on well-formed traffic.  ZKBATCH_NO_PREDICT=1 in the environment
+ * the kernel, and the batch is decoded again from that frame's chunk onwards with ordered
+ * look-back placement — same result, at most one extra decode kernel.  0 on well-formed traffic.  ZKBATCH_NO_PREDICT=1 in the environment
  * (read at zkb_ctx_create) turns the prediction off.  Diagnostic only. */
 uint64_t zkb_row_mispredicts(const zkb_ctx *ctx);
 /* Frames of the last decode call that were not well-formed (or reached past the staged

@@ -859,6 +859,7 @@ struct DecArgs {
 	uint64_t        n_frames;
 	zkb_decoded     o;
 	uint4          *lb;           /* [n_chunks] { state, stat rows, buf rows, acl rows } */
+	uint32_t        chunk0;       /* first chunk of this launch (a look-back pass may redo only the tail of a batch) */
 	zk_ctrl        *ctrl;
 };
 
@@ -1901,10 +1902,19 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 		const uint4 rb0 = a.g_rbase[g0], rb1 = a.g_rbase[g1 < a.n_gran ? g1 : a.n_gran];
 		e0 = rb0.x; e1 = rb0.y; e2 = rb0.z;
 		if (ts != rb1.x - rb0.x || tb != rb1.y - rb0.y || ta != rb1.z - rb0.z) {
-			if (lane == 0) atomicOr(&a.ctrl->error, ZK_DERR_MISPREDICT);
+			if (lane == 0) { atomicOr(&a.ctrl->error, ZK_DERR_MISPREDICT); atomicMin(&a.ctrl->first_bad, chunk); }
 			return;
 		}
-	} else if (chunk > 0) {
+	} else if (chunk == a.chunk0) {
+		/* a pass that redoes the tail of a batch starts from the predicted rows of its first
+		 * chunk: every chunk before it matched its prediction, so they are the real ones */
+		if (a.chunk0) { const uint4 seed = a.g_rbase[g0]; e0 = seed.x; e1 = seed.y; e2 = seed.z; }
+	} else {
+		uint4 seed = make_uint4(ZK_LB_PFX, 0, 0, 0);
+		if (a.chunk0) {
+			const uint4 rb = a.g_rbase[a.chunk0 << gsh];
+			seed.y = rb.x; seed.z = rb.y; seed.w = rb.z;
+		}
 		if (lane == 0) st_desc(a.lb + chunk, make_uint4(ZK_LB_AGG, ts, tb, ta));
 		/* Each round looks at the 128 chunks before position j: lane l reads chunks j-l,
 		 * j-32-l, j-64-l, j-96-l with four independent loads (one round trip).  It can finish
@@ -1916,8 +1926,8 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 #pragma unroll
 			for (int q = 0; q < 4; ++q) {
 				const int64_t idx = j - 32 * q - (int64_t)lane;
-				d[q] = make_uint4(ZK_LB_PFX, 0, 0, 0);
-				if (idx >= 0) d[q] = ld_desc(a.lb + idx);
+				d[q] = seed;                         /* everything before the launch's first chunk */
+				if (idx >= (int64_t)a.chunk0) d[q] = ld_desc(a.lb + idx);
 			}
 			bool done = false, wait = false;
 			int64_t hole_idx = 0;
@@ -2095,7 +2105,7 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(
 #else
 	const long long t0 = 0;
 #endif
-	const uint32_t chunk = blockIdx.x * ZK_DEC_WARPS + (threadIdx.x >> 5);
+	const uint32_t chunk = a.chunk0 + blockIdx.x * ZK_DEC_WARPS + (threadIdx.x >> 5);
 	if (chunk >= a.n_chunks) return;
 	if (lane == 0) mbar_init(bar, 1);
 	__syncwarp();
@@ -2350,26 +2360,35 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	const unsigned dec_blocks = (L.n_chunks + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS;
 	ZK_EV(ctx, 4);
 	bool lookback = ctx->no_predict != 0;
+	unsigned long long slow_first = 0;
+	bool have_slow = false;
 	if (!lookback) {
 		/* first try: every chunk places its rows where the splitter predicted */
+		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->first_bad, 0xFF, sizeof (unsigned int), ctx->stream));
 		k_decode<true><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
 		LAUNCH_CHECK(ctx);
 		if ((rc = zk_read_ctrl(ctx))) return rc;
 		if (ctx->h_ctrl->error == ZK_DERR_MISPREDICT) {
-			/* some frame is not what its header promised: same pass again, rows placed by look-back */
+			/* Some frame is not what its header promised.  Every chunk before the first one that
+			 * noticed has its rows in the right place (its own and all earlier counts matched);
+			 * the rest of the batch is done again, rows placed by look-back from there on. */
 			ctx->mispredicts++;
 			lookback = true;
+			da.chunk0 = ctx->h_ctrl->first_bad < L.n_chunks ? ctx->h_ctrl->first_bad : 0;
+			slow_first = ctx->h_ctrl->n_slow;      /* the first pass already saw every frame */
+			have_slow = true;
 			ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->error, 0, sizeof (unsigned int), ctx->stream));
-			ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long) * 9, ctx->stream));
 		}
 	}
 	if (lookback) {
-		ZK_CUDA(ctx, cudaMemsetAsync(da.lb, 0, (size_t)L.n_chunks * 16, ctx->stream));
-		k_decode<false><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		const uint32_t todo = L.n_chunks - da.chunk0;
+		ZK_CUDA(ctx, cudaMemsetAsync(da.lb + da.chunk0, 0, (size_t)todo * 16, ctx->stream));
+		k_decode<false><<<(todo + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
 		LAUNCH_CHECK(ctx);
 	}
 	ZK_EV(ctx, 5);
 	if (lookback && (rc = zk_read_ctrl(ctx))) return rc;
+	if (have_slow) ctx->h_ctrl->n_slow = slow_first;
 	if (ctx->timing) ZK_CUDA(ctx, cudaEventSynchronize(ctx->ev[5]));
 	if (ctx->timing) {
 		cudaEventElapsedTime(&ctx->phase_ms[0], ctx->ev[0], ctx->ev[1]);

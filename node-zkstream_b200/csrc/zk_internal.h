@@ -34,7 +34,7 @@
 struct zk_ctrl {
 	unsigned int       error;
 	unsigned int       n_dirty;     /* granules whose state changed in the last scan (dirty or re-selected) */
-	unsigned int       reserved0;   /* keeps n_dirty .. n_rewalk one 12-byte span (cleared together) */
+	unsigned int       first_bad;   /* k_decode<true>: lowest chunk whose rows differ from the prediction (cleared with n_dirty during the split) */
 	unsigned int       n_rewalk;    /* of those, granules that need a new walk */
 	unsigned long long n_frames;
 	unsigned long long n_stat, n_buf, n_acl;

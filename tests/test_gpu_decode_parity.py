@@ -372,3 +372,25 @@ def test_row_prediction_and_its_fallback(ctx, oracle, synth, zk, monkeypatch):
         assert ctx2.row_mispredicts == 0
     finally:
         ctx2.close()
+
+
+@pytest.mark.parametrize("where", [0.0, 0.37, 0.999])
+def test_partial_redo_after_a_mispredicted_chunk(ctx, oracle, synth, zk, where):
+    """One damaged reply (its child count lies) somewhere in ~60 MB of clean traffic: the rows
+    before it stay where the first pass put them, the rest is redone with the look-back."""
+    pc = synth.native_cfg2(23, 8, 20000)
+    n = pc.nsessions
+    xt = pc.xidtable()
+    cols = oracle.decode(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt)
+    gc2 = np.nonzero((cols.opcode == 12) & (cols.err == 0) & (cols.a0 > 2))[0]
+    f = int(gc2[min(len(gc2) - 1, int(where * len(gc2)))])
+    data = pc.rsp.copy()
+    pos = int(cols.frame_off[f]) + 4 + 16                      # the child count of that GET_CHILDREN2 reply
+    data[pos:pos + 4] = np.frombuffer((int(cols.a0[f]) + 1).to_bytes(4, "big"), dtype=np.uint8)
+    before = ctx.row_mispredicts
+    g = ctx.decode_host(data, pc.rsp_off, pc.rsp_flags, None, xt)
+    o = oracle.decode(data, pc.rsp_off, pc.rsp_flags, None, xt)
+    assert g.diff(o) == []
+    assert ctx.row_mispredicts == before + 1
+    assert int(o.status[f]) == 1                               # the damaged frame is BAD_DECODE, everything else as before
+    assert ctx.last_slow_frames >= 1
