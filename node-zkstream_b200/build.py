@@ -52,7 +52,8 @@ def build(force=False, verbose=False):
         cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, s), "-o", o]
         subprocess.run(cmd, check=True)
         objs.append(o)
-    subprocess.run([NVCC, "-shared", "--cudart", "shared", "-o", LIB] + objs, check=True)
+    subprocess.run([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "--cudart", "shared", "-o", LIB] + objs,
+                   check=True)
     return LIB
 
 

@@ -11,5 +11,5 @@ for s in zk_ctx zk_decode zk_encode zk_stats; do
   /usr/local/cuda/bin/nvcc $F "$@" -c $C/$s.cu -o /tmp/zkv_$name/$s.o &
 done
 wait
-/usr/local/cuda/bin/nvcc -shared --cudart shared -o tools/libzkbatch_$name.so /tmp/zkv_$name/*.o
+/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared --cudart shared -o tools/libzkbatch_$name.so /tmp/zkv_$name/*.o
 echo tools/libzkbatch_$name.so
