@@ -370,3 +370,32 @@ def test_encode_dev_matches_host_variant(ctx, oracle):
     assert np.array_equal(fo.cpu().numpy().view(np.uint64), ho) and np.array_equal(st[:len(pkts)].cpu().numpy(), hs)
     _, _, _, need, rc = dev.encode_dev(ctx, dr, hd.size - 1)
     assert rc == zk._abi.EOVERFLOW and need == hd.size
+
+
+def test_replay_host_with_damaged_frames(ctx, oracle, synth):
+    """The pipelined replay with a few lying child counts and a truncated session in the reply
+    streams: slices that contain them take the two-pass route, the result is still the oracle's."""
+    shard = importlib.import_module("node-zkstream_b200.shard")
+    pc = synth.native_cfg2(77, 24, 1500)
+    n = pc.nsessions
+    layout = zk.XidTable(np.zeros(n, np.int32), np.full(n, pc.frames, np.uint32))
+    want_req = oracle.decode(pc.req, pc.req_off, pc.req_flags, None, None)
+    xt = oracle.xidtab_build(want_req, layout)
+    clean = oracle.decode(pc.rsp, pc.rsp_off, pc.rsp_flags, None, xt)
+    rsp = pc.rsp.copy()
+    gc2 = np.nonzero((clean.opcode == 12) & (clean.err == 0) & (clean.a0 > 1))[0]
+    for f in gc2[:: max(1, len(gc2) // 7)][:7]:
+        pos = int(clean.frame_off[f]) + 4 + 16
+        rsp[pos:pos + 4] = np.frombuffer((int(clean.a0[f]) + 3).to_bytes(4, "big"), dtype=np.uint8)
+    rsp[int(pc.rsp_off[5]) + 100000:int(pc.rsp_off[6])] = 0xEE       # session 5: garbage tail -> BAD_LENGTH
+    want_rsp = oracle.decode(rsp, pc.rsp_off, pc.rsp_flags, None, xt)
+    assert int(want_rsp.sess_bad_length_at[5]) != zk._abi.NO_OFFSET
+    before = ctx.row_mispredicts
+    for slice_bytes in (0, 1 << 20):
+        got = []
+        ctx.replay_host(pc.req, pc.req_off, rsp, pc.rsp_off, layout.base, layout.count,
+                        lambda first, ns, rq, rs: got.append((first, ns, rq, rs)), slice_bytes=slice_bytes)
+        zeros = [0] * len(got)
+        assert shard.merge([g[2] for g in got], zeros, zeros).diff(want_req) == []
+        assert shard.merge([g[3] for g in got], zeros, zeros).diff(want_rsp) == []
+    assert ctx.row_mispredicts > before
