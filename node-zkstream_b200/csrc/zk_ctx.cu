@@ -272,13 +272,14 @@ ZKB_EXPORT int zkb_decode_host(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbyt
 	uint64_t n_frames = 0;
 	if ((rc = zk_split_device(ctx, d_bytes, nbytes, &dsess, have_xid ? &dxid : NULL, &n_frames))) return rc;
 
-	/* side tables: a Stat needs >= 88 input bytes, a buffer row >= 4; start from what typical
-	 * traffic needs and re-run phase B with the exact counts if that was too small */
-	uint64_t cs = n_frames < nbytes / 88 + 1 ? n_frames : nbytes / 88 + 1;
-	uint64_t cb = n_frames * 2 + nbytes / 64 + 16;
-	if (cb > nbytes / 4 + 1) cb = nbytes / 4 + 1;
-	uint64_t ca = n_frames / 2 + 16;
-	if (ca > nbytes / 12 + 1) ca = nbytes / 12 + 1;
+	/* the splitter's row prediction is exact for well-formed traffic; a batch it got wrong
+	 * comes back with ZKB_EOVERFLOW and the true counts, and is decoded once more */
+	uint64_t cs = ctx->pred_rows[0] + 16, cb = ctx->pred_rows[1] + 16, ca = ctx->pred_rows[2] + 16;
+	if (nbytes == 0) cs = cb = ca = 16;
+	/* a damaged count field can promise anything: no more rows than the bytes could hold */
+	if (cs > nbytes / 68 + 16) cs = nbytes / 68 + 16;
+	if (cb > nbytes / 4 + 16) cb = nbytes / 4 + 16;
+	if (ca > nbytes / 12 + 16) ca = nbytes / 12 + 16;
 	zkb_decoded dv;
 	for (int attempt = 0;; ++attempt) {
 		memset(&dv, 0, sizeof (dv));
@@ -500,11 +501,14 @@ static int replay_decode_dir(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbyt
 	uint64_t n_frames = 0;
 	const uint32_t nsess = ds->nsessions;
 	if ((rc = zk_split_device(ctx, d_bytes, nbytes, ds, dx, &n_frames))) return rc;
-	uint64_t cs = n_frames < nbytes / 88 + 1 ? n_frames : nbytes / 88 + 1;
-	uint64_t cb = n_frames * 2 + nbytes / 64 + 16;
-	if (cb > nbytes / 4 + 1) cb = nbytes / 4 + 1;
-	uint64_t ca = n_frames / 2 + 16;
-	if (ca > nbytes / 12 + 1) ca = nbytes / 12 + 1;
+	/* the splitter's row prediction is exact for well-formed traffic; a batch it got wrong
+	 * comes back with ZKB_EOVERFLOW and the true counts, and is decoded once more */
+	uint64_t cs = ctx->pred_rows[0] + 16, cb = ctx->pred_rows[1] + 16, ca = ctx->pred_rows[2] + 16;
+	if (nbytes == 0) cs = cb = ca = 16;
+	/* a damaged count field can promise anything: no more rows than the bytes could hold */
+	if (cs > nbytes / 68 + 16) cs = nbytes / 68 + 16;
+	if (cb > nbytes / 4 + 16) cb = nbytes / 4 + 16;
+	if (ca > nbytes / 12 + 16) ca = nbytes / 12 + 16;
 	for (int attempt = 0;; ++attempt) {
 		memset(dv, 0, sizeof (*dv));
 		size_t need = carve_decoded(dv, NULL, n_frames, cs, cb, ca, nsess);

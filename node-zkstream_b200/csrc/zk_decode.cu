@@ -788,7 +788,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	a.g_carry[g] = carry;
 	a.g_base[g] = ex.c;
 	a.g_rbase[g] = make_uint4(ex.r0, ex.r1, ex.r2, 0);
-	if (g == a.n_gran - 1) a.g_rbase[a.n_gran] = make_uint4(ex.r0 + x.r0, ex.r1 + x.r1, ex.r2 + x.r2, 0);
+	if (g == a.n_gran - 1) {
+		a.g_rbase[a.n_gran] = make_uint4(ex.r0 + x.r0, ex.r1 + x.r1, ex.r2 + x.r2, 0);
+		a.ctrl->pred_rows[0] = ex.r0 + x.r0; a.ctrl->pred_rows[1] = ex.r1 + x.r1; a.ctrl->pred_rows[2] = ex.r2 + x.r2;
+	}
 	a.g_src[g] = (ex.v == ZK_INHERIT) ? 0u : ex.src;
 	a.g_ssrc[g] = ex.ssrc;
 	/* a walk is consistent with the carry iff both name the same in-granule position, or
@@ -2301,6 +2304,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		}
 	}
 	*n_frames = ctx->h_ctrl->n_frames;
+	for (int k = 0; k < 3; ++k) ctx->pred_rows[k] = ctx->h_ctrl->pred_rows[k];
 	memcpy(ctx->split_prof, ctx->h_ctrl->prof, sizeof (ctx->split_prof));
 	return ZKB_OK;
 }
