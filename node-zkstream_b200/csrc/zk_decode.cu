@@ -223,6 +223,9 @@ __device__ __forceinline__ int32_t win_be32(const uint4 &a, const uint4 &b, cons
 #ifndef ZK_GUESS_HOPS
 #define ZK_GUESS_HOPS 3
 #endif
+#ifndef ZK_GUESS_HOPS_SERVER
+#define ZK_GUESS_HOPS_SERVER 1   /* requests: the local test already checks the path */
+#endif
 struct GuessCtx {
 	const uint8_t *bytes;
 	uint64_t lim, send;
@@ -243,6 +246,14 @@ __device__ __forceinline__ uint32_t guess_at(const GuessCtx &g, uint64_t blk, ui
 	if (p + 4 + (uint64_t)len > g.send) return 0;
 	const int32_t f = g.server ? win_be32<K + 8>(v0, v1, v2) : win_be32<K + 16>(v0, v1, v2);
 	if (g.server ? !op_known(f) : !err_known(f)) return 0;
+#ifndef ZK_GUESS_NO_PATHCHECK
+	/* a request that carries a path has its length next and '/' as its first byte; a real frame
+	 * that fails this (an empty path) only costs the granule a fix-up */
+	if (g.server && ((f >= 1 && f <= 6) || f == 8 || f == 9 || f == 12)) {
+		const int32_t pl = win_be32<K + 12>(v0, v1, v2);
+		if (pl < 1 || pl + 12 > len || ((uint32_t)win_be32<K + 16>(v0, v1, v2) >> 24) != 0x2fu) return 0;
+	}
+#endif
 	return 1u << K;
 }
 
@@ -310,7 +321,7 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 				cand &= cand - 1;
 				const uint64_t p = seg + 64 * half + (uint64_t)k;
 				const int32_t len = (int32_t)g_be32(a.bytes, p);
-				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, ZK_GUESS_HOPS)) {
+				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS)) {
 #ifdef ZK_PROFILE_PHASES
 					atomicAdd(&a.ctrl->prof[3], (unsigned long long)(clock64() - gp_t0));
 #endif
