@@ -123,3 +123,117 @@ for (var s = 0; s < %d; ++s) {
     for got, ref in zip(lines, g):
         assert got["maxZxid"] == ref["all"]["maxZxid"]
         assert got["counts"] == ref["all"]["counts"]
+
+
+def _cols_js(cols, zk, consumed):
+    parts = []
+    for name, dt in zk._abi.FRAME_COLS + zk._abi.STAT_COLS + zk._abi.BUF_COLS + zk._abi.ACL_COLS + zk._abi.SESS_COLS:
+        a = getattr(cols, name)
+        parts.append("%s:%s" % (name, js_array64(a) if dt in ("i8", "u8") else js_array(a)))
+    parts.append("n_frames:%d,n_stat:%d,n_buf:%d,n_acl:%d,consumed:%d" % (cols.n_frames, cols.n_stat, cols.n_buf,
+                                                                       cols.n_acl, consumed))
+    return "{" + ",".join(parts) + "}"
+
+
+def test_js_batch_decode_stream_with_recorded_addon(oracle, synth, zk):
+    """js/batch-streams.js (the drop-in ZKDecodeStream) run in the reference's engine against a
+    recorded addon: every decodeHost call the stream makes is answered with the columns the
+    oracle gives for exactly those bytes, so what is tested is the stream's own logic - carrying
+    incomplete frames over, the handshake state per call, the xid table it builds from
+    fsm.zcf_xidMap, packets pushed and errors emitted in order, getting stuck after BAD_LENGTH -
+    against what the reference's ZKDecodeStream did with the same bytes (ref_decode.json)."""
+    import random
+    from _canon import canon_events
+    g = json.load(open(os.path.join(GOLD, "ref_decode.json")))["sessions"]
+    rng = random.Random(5)
+    chosen = []
+    for s in g:
+        ev = s["events"]
+        data = bytes.fromhex(s["hex"])
+        if s["hs"] != 1 or len(ev) < 2 or "pkt" not in ev[0] or len(data) < 8:
+            continue
+        first = 4 + int.from_bytes(data[:4], "big")
+        if first >= len(data):
+            continue
+        chosen.append((s, data, first))
+    chosen = chosen[:60]
+    assert len(chosen) >= 30
+    table, sess_js = {}, []
+    for s, data, first in chosen:
+        cuts = sorted(set([first] + [rng.randrange(first, len(data)) for _ in range(rng.randrange(0, 4))]))
+        chunks = [data[a:b] for a, b in zip([0] + cuts, cuts + [len(data)]) if b > a]
+        xm = {int(k): v for k, v in s["xidMap"].items()}
+        xt = zk.XidTable.from_maps([xm]) if not s["isServer"] else None
+        flags = np.array([zk._abi.SESS_SERVER if s["isServer"] else 0], dtype=np.uint8)
+        carry, stuck = b"", False
+        for i, ch in enumerate(chunks):
+            if stuck:
+                break
+            pend = carry + ch
+            hsv = np.array([0xFFFFFFFF if i == 0 else 0], dtype=np.uint32)
+            cols = oracle.decode(np.frombuffer(pend, dtype=np.uint8), None, flags, hsv, xt)
+            consumed = int(cols.sess_consumed[0])
+            table[pend.hex() + ("S" if s["isServer"] else "C") + ("H" if i == 0 else "N")] = _cols_js(cols, zk, consumed)
+            stuck = int(cols.sess_bad_length_at[0]) != zk._abi.NO_OFFSET
+            carry = pend[consumed:]
+        names = {str(k): zk.consts.OP_CODE_LOOKUP[v] for k, v in xm.items()}
+        sess_js.append("{isServer:%s,xidMap:%s,chunks:[%s]}" % (
+            "true" if s["isServer"] else "false", json.dumps(names), ",".join(json.dumps(c.hex()) for c in chunks)))
+    src = {n: open(os.path.join(ROOT, "node-zkstream_b200", "js", n)).read()
+           for n in ("materialise.js", "flatten.js", "batch-streams.js")}
+    driver = "\n".join([
+        "var TABLE = {" + ",".join("%s:%s" % (json.dumps(k), v) for k, v in table.items()) + "};",
+        "function Int8Array(n) { var a = []; for (var i = 0; i < n; ++i) a.push(0); return a; }",
+        "Buffer.concat = function (list, total) { var h = ''; for (var i = 0; i < list.length; ++i) h += list[i].toString('hex'); return new Buffer(h, 'hex'); };",
+        src["materialise.js"], src["flatten.js"],
+        "var CUR = { server: false, hs: true };",
+        "var fakeAddon = { createContext: function () { return {}; }, decodeHost: function (ctx, data, isServer, hs, ops) {",
+        "  var key = data.toString('hex') + (isServer ? 'S' : 'C') + (hs ? 'H' : 'N');",
+        "  if (!TABLE[key]) throw new Error('unrecorded decodeHost call ' + key.slice(-40));",
+        "  CUR.ops = ops; return TABLE[key]; } };",
+        "DEFS['batch-streams'] = function (module, exports, require) {\n" + src["batch-streams.js"] + "\n};",
+        r"""
+function req2(name) {
+	if (name === 'zkstream/lib/zk-consts') return requireShim('./zk-consts');
+	if (name === 'zkstream/lib/errors') return requireShim('./errors');
+	if (name === 'zkstream/lib/jute-buffer') return requireShim('./jute-buffer');
+	if (name === './build/Release/zkbatch_napi.node') return fakeAddon;
+	if (name === './materialise') return { makeMaterialiser: makeMaterialiser };
+	if (name === './flatten') return { makeFlatten: makeFlatten };
+	return requireShim(name);
+}
+var bm = { exports: {} };
+DEFS['batch-streams'](bm, bm.exports, req2);
+var BatchDecode = bm.exports.ZKDecodeStream;
+var consts = requireShim('./zk-consts');
+for (var si = 0; si < SESS.length; ++si) {
+	var sess = SESS[si], calls = 0;
+	var fsm = { zcf_xidMap: sess.xidMap, isInState: function (st) { return (st === 'handshaking' && calls === 0); } };
+	var ds = new BatchDecode({ fsm: fsm, isServer: sess.isServer });
+	var out = [], opsOk = true;
+	for (var i = 0; i < sess.chunks.length; ++i) {
+		var called = false;
+		ds._transform(hex(sess.chunks[i]), null, function () { called = true; });
+		calls++;
+		if (!sess.isServer) {
+			/* the table handed to the addon must say what fsm.zcf_xidMap says */
+			for (var k in sess.xidMap) if (parseInt(k, 10) >= 0 && CUR.ops[parseInt(k, 10)] !== consts.OP_CODES[sess.xidMap[k]]) opsOk = false;
+		}
+		if (!called) break;            /* BAD_LENGTH: stuck, as the reference is */
+	}
+	for (var e = 0; e < ds._events.length; ++e) {
+		var ev = ds._events[e];
+		if (ev.push !== undefined) out.push('{"pkt":' + canon(ev.push) + '}');
+		else if (ev.ev === 'error') out.push('{"error":{"code":' + jstr(ev.arg.code) + ',"message":' + jstr(ev.arg.message) + '}}');
+	}
+	print('{"opsOk":' + (opsOk ? 'true' : 'false') + ',"events":[' + out.join(',') + ']}');
+}
+"""])
+    driver = "var SESS = [" + ",".join(sess_js) + "];\n" + driver
+    out = ref_js.run_js(driver)
+    lines = [l for l in out.splitlines() if l.strip()]
+    assert len(lines) == len(chosen)
+    for line, (s, _, _) in zip(lines, chosen):
+        got = ref_js._decanon(json.loads(line))
+        assert got["opsOk"] is True
+        assert canon_events(got["events"]) == s["events"], s["corpus"]
