@@ -11,8 +11,8 @@
  * reference).
  *
  * Needs a node with N-API (>= 8.x) and the built addon; neither exists in the build image,
- * so the decode stream is exercised in the reference's own JavaScript engine against a
- * recorded addon (tests/test_js_shim.py); the encode stream only through flatten.js.
+ * so both streams are exercised in the reference's own JavaScript engine against a recorded
+ * addon (tests/test_js_shim.py).
  */
 var mod_stream = require('stream');
 var mod_util = require('util');

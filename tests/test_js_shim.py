@@ -237,3 +237,64 @@ for (var si = 0; si < SESS.length; ++si) {
         got = ref_js._decanon(json.loads(line))
         assert got["opsOk"] is True
         assert canon_events(got["events"]) == s["events"], s["corpus"]
+
+
+def test_js_batch_encode_stream_with_recorded_addon(oracle, zk):
+    """js/batch-streams.js ZKEncodeStream in the reference's engine: the packet goes through
+    flatten.js, the recorded addon returns what the oracle encodes for the same descriptors, and the
+    stream must push the reference's frame, record xid -> opcode in fsm.zcf_xidMap, or throw the
+    reference's 'Unsupported opcode' error (tests/golden/ref_encode.json)."""
+    from test_oracle_golden import unjson
+    g = json.load(open(os.path.join(GOLD, "ref_encode.json")))["packets"]
+    recs = []
+    for p in g:
+        pkt = unjson(p["pkt"])
+        batch = zk.RequestBatch.from_packets([pkt], p["handshaking"], p["isServer"])
+        data, fo, st = oracle.encode(batch)
+        recs.append("{bytes:hex(%s),frame_off:%s,status:%s}" % (json.dumps(data.tobytes().hex()), js_array(fo), js_array(st)))
+    src = {n: open(os.path.join(ROOT, "node-zkstream_b200", "js", n)).read()
+           for n in ("materialise.js", "flatten.js", "batch-streams.js")}
+    cases = ",".join("{hs:%s,server:%s,pkt:%s}" % ("true" if p["handshaking"] else "false",
+                                                   "true" if p["isServer"] else "false",
+                                                   ref_js.js_literal(unjson(p["pkt"]))) for p in g)
+    driver = "\n".join([
+        "var RECS = [" + ",".join(recs) + "]; var CASES = [" + cases + "]; var NEXT = 0;",
+        "function Int8Array(n) { var a = []; for (var i = 0; i < n; ++i) a.push(0); return a; }",
+        "Buffer.concat = function (list, total) { var h = ''; for (var i = 0; i < list.length; ++i) h += list[i].toString('hex'); return new Buffer(h, 'hex'); };",
+        src["materialise.js"], src["flatten.js"],
+        "var fakeAddon = { createContext: function () { return {}; }, encodeColumns: function (ctx, cols) { return RECS[NEXT]; } };",
+        "DEFS['batch-streams'] = function (module, exports, require) {\n" + src["batch-streams.js"] + "\n};",
+        r"""
+function req2(name) {
+	if (name === 'zkstream/lib/zk-consts') return requireShim('./zk-consts');
+	if (name === 'zkstream/lib/errors') return requireShim('./errors');
+	if (name === 'zkstream/lib/jute-buffer') return requireShim('./jute-buffer');
+	if (name === './build/Release/zkbatch_napi.node') return fakeAddon;
+	if (name === './materialise') return { makeMaterialiser: makeMaterialiser };
+	if (name === './flatten') return { makeFlatten: makeFlatten };
+	return requireShim(name);
+}
+var bm = { exports: {} };
+DEFS['batch-streams'](bm, bm.exports, req2);
+for (NEXT = 0; NEXT < CASES.length; ++NEXT) {
+	var cs = CASES[NEXT];
+	var fsm = { zcf_xidMap: {}, isInState: function (st) { return (st === 'handshaking' && cs.hs); } };
+	var es = new bm.exports.ZKEncodeStream({ fsm: fsm, isServer: cs.server });
+	var res;
+	try {
+		es._transform(cs.pkt, null, function () {});
+		res = '{"frame":"' + es._pushed[0].toString('hex') + '"}';
+	} catch (e) {
+		res = '{"throw":' + jstr(String(e.name) + ': ' + String(e.message)) + '}';
+	}
+	var xm = [];
+	for (var k in fsm.zcf_xidMap) xm.push(jstr(k) + ':' + jstr(String(fsm.zcf_xidMap[k])));
+	print('{"result":' + res + ',"xidMap":{' + xm.join(',') + '}}');
+}
+"""])
+    out = ref_js.run_js(driver)
+    lines = [json.loads(l) for l in out.splitlines() if l.strip()]
+    assert len(lines) == len(g)
+    for got, p in zip(lines, g):
+        assert got["result"] == p["result"], p["pkt"]
+        assert got["xidMap"] == {k: v for k, v in p["xidMap"].items() if v is not None}, p["pkt"]
