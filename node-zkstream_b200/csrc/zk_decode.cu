@@ -826,10 +826,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 }
 
 /* checks off[0] == 0, off[n] == nbytes, monotone */
-__global__ void k_check_sessions(const uint64_t *off, uint32_t nsess, uint64_t nbytes, zk_ctrl *ctrl)
+__global__ void k_check_sessions(const uint64_t *off, const uint8_t *flags, uint32_t nsess, uint64_t nbytes,
+    zk_ctrl *ctrl)
 {
 	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i > nsess) return;
+	if (i < nsess) {
+		const unsigned int bit = (flags && (flags[i] & ZKB_SESS_SERVER)) ? 1u : 2u;
+		if (!(ctrl->dir_mask & bit)) atomicOr(&ctrl->dir_mask, bit);
+	}
 	bool bad = false;
 	if (i == 0 && off[0] != 0) bad = true;
 	if (i == nsess && off[i] != nbytes) bad = true;
@@ -1239,6 +1244,9 @@ __device__ void parse_request(Cur &c, Parsed &p, int &opcode)
 }
 
 /* handlePacket (zk-streams.js:66-99) for one frame; no side rows are written here */
+/* DIR: 1 = every session of the batch is client->server, 2 = every one is server->client,
+ * 0 = look at the session's flag.  The one-direction kernels carry only that direction's readers. */
+template <int DIR>
 __device__ void parse_frame(const Rd &rd, const DecArgs &a, uint64_t foff, int32_t flen,
     uint32_t s, uint32_t idx_in_session, Parsed &p)
 {
@@ -1248,7 +1256,7 @@ __device__ void parse_frame(const Rd &rd, const DecArgs &a, uint64_t foff, int32
 	p.n_stat = p.n_buf = p.n_acl = 0; p.n_fixed = 0; p.vec_kind = VEC_NONE;
 	p.stat_pos = 0; p.vec_pos = 0;
 	p.fb0_pos = p.fb1_pos = 0; p.fb0_len = p.fb1_len = 0;
-	const bool server = a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER);
+	const bool server = DIR == 1 ? true : DIR == 2 ? false : (a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER));
 	const uint32_t hs = a.sess_hs ? __ldg(a.sess_hs + s) : 1u;
 	int opcode = ZKB_OP_NONE;
 	uint32_t kind;
@@ -1629,7 +1637,7 @@ __device__ unsigned long long zk_hist[3][64];
 
 /* Everything one warp does for one 8 KiB chunk.  `phase` is the parity of the warp's
  * mbarrier for this use (it flips every chunk). */
-template <bool PRED>
+template <bool PRED, int DIR>
 __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
     const uint32_t chunk, const uint32_t lane, const long long zk_t0)
 {
@@ -1855,7 +1863,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 		a.o.frame_len[f] = flen;
 		a.o.session[f] = s;
 		const bool inwin = rel + 4u + (uint32_t)flen <= wlen;
-		const bool server = a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER);
+		const bool server = DIR == 1 ? true : DIR == 2 ? false : (a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER));
 		const uint32_t hs = a.sess_hs ? __ldg(a.sess_hs + s) : 1u;
 		const uint32_t idx = f - first;
 		FrameCols o;
@@ -1872,7 +1880,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 		if (done != 1) {
 			Parsed p;
 			n_slow++;
-			parse_frame(rd, a, foff, flen, s, idx, p);
+			parse_frame<DIR>(rd, a, foff, flen, s, idx, p);
 			o.meta = p.meta; o.xid = p.xid; o.zxid = p.zxid; o.err = p.err; o.a0 = p.a0; o.a1 = p.a1;
 			if (p.n_stat | p.n_buf | p.n_acl) {
 				if (inwin) {
@@ -2106,7 +2114,7 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 #ifndef ZK_DEC_MINBLOCKS
 #define ZK_DEC_MINBLOCKS 5
 #endif
-template <bool PRED>
+template <bool PRED, int DIR>
 __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(DecArgs a)
 {
 	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
@@ -2123,7 +2131,7 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(
 	if (chunk >= a.n_chunks) return;
 	if (lane == 0) mbar_init(bar, 1);
 	__syncwarp();
-	decode_chunk<PRED>(a, c, bar, 0, chunk, lane, t0);
+	decode_chunk<PRED, DIR>(a, c, bar, 0, chunk, lane, t0);
 }
 
 /* ================================================================================== */
@@ -2262,7 +2270,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	}
 	const uint32_t nsess = sess->nsessions;
 	ZK_CUDA(ctx, cudaMemsetAsync(ctx->d_ctrl, 0, sizeof (zk_ctrl), ctx->stream));
-	k_check_sessions<<<(nsess + 1 + 255) / 256, 256, 0, ctx->stream>>>(sess->off, nsess, nbytes,
+	k_check_sessions<<<(nsess + 1 + 255) / 256, 256, 0, ctx->stream>>>(sess->off, sess->flags, nsess, nbytes,
 	    ctx->d_ctrl);
 	LAUNCH_CHECK(ctx);
 	if (nbytes == 0) {
@@ -2316,6 +2324,7 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	}
 	*n_frames = ctx->h_ctrl->n_frames;
 	for (int k = 0; k < 3; ++k) ctx->pred_rows[k] = ctx->h_ctrl->pred_rows[k];
+	ctx->dir = ctx->h_ctrl->dir_mask == 1u ? 1 : ctx->h_ctrl->dir_mask == 2u ? 2 : 0;
 	memcpy(ctx->split_prof, ctx->h_ctrl->prof, sizeof (ctx->split_prof));
 	return ZKB_OK;
 }
@@ -2380,7 +2389,9 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	if (!lookback) {
 		/* first try: every chunk places its rows where the splitter predicted */
 		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->first_bad, 0xFF, sizeof (unsigned int), ctx->stream));
-		k_decode<true><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		if (ctx->dir == 1) k_decode<true, 1><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		else if (ctx->dir == 2) k_decode<true, 2><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		else k_decode<true, 0><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
 		LAUNCH_CHECK(ctx);
 		if ((rc = zk_read_ctrl(ctx))) return rc;
 		if (ctx->h_ctrl->error == ZK_DERR_MISPREDICT) {
@@ -2398,7 +2409,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	if (lookback) {
 		const uint32_t todo = L.n_chunks - da.chunk0;
 		ZK_CUDA(ctx, cudaMemsetAsync(da.lb + da.chunk0, 0, (size_t)todo * 16, ctx->stream));
-		k_decode<false><<<(todo + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		k_decode<false, 0><<<(todo + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
 		LAUNCH_CHECK(ctx);
 	}
 	ZK_EV(ctx, 5);

@@ -41,7 +41,8 @@ struct zk_ctrl {
 	unsigned long long enc_bytes;
 	unsigned long long n_slow;   /* frames that needed the generic (exact) parser */
 	unsigned long long prof[8];  /* ZK_PROFILE_PHASES builds: cycles per decode phase, chunk count */
-	unsigned int       pred_rows[4]; /* the splitter's predicted STAT / BUF / ACL row totals of the batch */
+	unsigned int       pred_rows[3]; /* the splitter's predicted STAT / BUF / ACL row totals of the batch */
+	unsigned int       dir_mask;     /* 1 = some session is client->server, 2 = some is server->client (k_check_sessions) */
 };
 
 struct zkb_ctx {
@@ -52,6 +53,7 @@ struct zkb_ctx {
 	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
 	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
 	int           no_predict;     /* ZKBATCH_NO_PREDICT=1: always place side rows by look-back */
+	int           dir;            /* batch split last: 1 = only client->server streams, 2 = only server->client, 0 = both */
 	uint64_t      pred_rows[3];   /* predicted side-table rows of the batch split last (exact for well-formed traffic) */
 	uint64_t      mispredicts;    /* decode passes repeated with the look-back because a row prediction failed */
 	unsigned long long prof[8];
