@@ -387,8 +387,13 @@ int zkb_xidtab_build_dev(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsession
  * finished.  Results are identical to zkb_xidtab_build_dev.
  *   - layout->nops above ZKB_NOALLOC_MAX_XIDS is refused with ZKB_ERANGE (text in errbuf);
  *     cover more xids by building the table for a few sessions per call.
- *   - The first call on each GPU looks up where the array lives on that GPU; make that
- *     first call outside any stream capture.
+ *   - The call waits for its own work (it ends with a stream synchronize), so it can never
+ *     be part of a stream capture; the first call on each GPU also looks up where the array
+ *     lives on that GPU.  With lazy module loading that first call is also the moment the
+ *     8 MiB are claimed on that GPU: make one warm-up call per GPU at start-up, before the
+ *     pool takes the rest of the memory.  The address is remembered per device ordinal for
+ *     the life of the process; after cudaDeviceReset the process must be restarted.
+ *   - A layout entry that points past the table (off[s] + count[s] > nops) is ignored.
  *   - Every call uses the same array (a call clears the slots it is about to use), so two
  *     calls whose GPU work overlaps, from any threads or streams, corrupt each other: run
  *     them one after the other.

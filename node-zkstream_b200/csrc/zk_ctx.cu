@@ -516,6 +516,8 @@ static int replay_decode_dir(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbyt
 		carve_decoded(dv, out_base, n_frames, cs, cb, ca, nsess);
 		rc = zk_fields_device(ctx, d_bytes, nbytes, ds, dx, n_frames, dv);
 		if (rc == ZKB_EOVERFLOW && attempt == 0) { cs = dv->n_stat; cb = dv->n_buf; ca = dv->n_acl; continue; }
+		/* still too small: tell the caller what the true row counts need, so it grows enough */
+		if (rc == ZKB_EOVERFLOW) *used = carve_decoded(dv, NULL, n_frames, dv->n_stat + 16, dv->n_buf + 16, dv->n_acl + 16, nsess);
 		if (rc) return rc;
 		*used = need;
 		return ZKB_OK;

@@ -2138,7 +2138,7 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(
 /* xid -> opcode table from a decoded request stream                                   */
 
 __global__ void k_xid_scatter(const zkb_decoded req, uint64_t n_frames, uint32_t nsess,
-    const int32_t *base, const uint32_t *count, const uint64_t *off, unsigned long long *tmp)
+    const int32_t *base, const uint32_t *count, const uint64_t *off, unsigned long long *tmp, uint64_t nops)
 {
 	uint64_t f = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (f >= n_frames) return;
@@ -2151,7 +2151,11 @@ __global__ void k_xid_scatter(const zkb_decoded req, uint64_t n_frames, uint32_t
 	if (idx < 0 || idx >= (int64_t)count[s]) return;
 	/* zcf_xidMap[xid] = opcode, last write wins (zk-streams.js:145): keep the highest frame */
 	unsigned long long key = ((f + 1) << 8) | (unsigned long long)((m >> 8) & 0xff);
-	atomicMax(tmp + off[s] + (uint64_t)idx, key);
+	/* the layout arrays are the caller's device memory, which the host cannot inspect: an entry
+	 * that points past the table (off + count > nops) is dropped, never written */
+	const uint64_t slot = off[s] + (uint64_t)idx;
+	if (slot >= nops) return;
+	atomicMax(tmp + slot, key);
 }
 
 __global__ void k_xid_finish(const unsigned long long *tmp, uint64_t n, int8_t *ops)
@@ -2463,7 +2467,7 @@ int zk_xidtab_build_device(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessi
 	ZK_CUDA(ctx, cudaMemsetAsync(tmp, 0, n * 8, ctx->stream));
 	if (req->n_frames) {
 		k_xid_scatter<<<(unsigned)((req->n_frames + 255) / 256), 256, 0, ctx->stream>>>(*req,
-		    req->n_frames, nsessions, layout->base, layout->count, layout->off, tmp);
+		    req->n_frames, nsessions, layout->base, layout->count, layout->off, tmp, n);
 		LAUNCH_CHECK(ctx);
 	}
 	k_xid_finish<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(tmp, n, d_ops_out);
@@ -2540,7 +2544,7 @@ int zkb_xidtab_build_noalloc(const zkb_decoded *req, uint32_t nsessions, const z
 	if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "cudaMemsetAsync", e);
 	if (req->n_frames) {
 		k_xid_scatter<<<(unsigned)((req->n_frames + 255) / 256), 256, 0, st>>>(*req, req->n_frames, nsessions,
-		    layout->base, layout->count, layout->off, slots);
+		    layout->base, layout->count, layout->off, slots, n);
 		e = cudaGetLastError();
 		if (e != cudaSuccess) return zk_noalloc_fail(errbuf, errcap, ZKB_ECUDA, "k_xid_scatter launch", e);
 	}
