@@ -671,6 +671,117 @@ double zko_bench_decode(const uint8_t *bytes, uint64_t nbytes, const zkb_session
 	return (t1.tv_sec - t0.tv_sec) + (t1.tv_nsec - t0.tv_nsec) * 1e-9;
 }
 
+/* ---- whole-batch digest (bench.py's parity gate on the corpus it times) ------------------
+ *
+ * Decodes the batch on `nthreads` threads (contiguous session ranges, in place) and folds every
+ * output column into one order-sensitive 64-bit digest:
+ *     D(col) = sum over rows i of mix64(value_i zero-extended to 64 bits) * (i + 1)   (mod 2^64)
+ * bench.py computes the same sums over the GPU's columns with integer tensor arithmetic; equal
+ * digests for all 29 columns = same rows in the same places.  out_digest order: the FRAMES, STAT,
+ * BUF, ACL columns as declared in zkb_decoded, then sess_consumed, sess_bad_length_at,
+ * sess_first_frame[nsessions + 1].  out_counts = { frames, stat, buf, acl }.
+ */
+static inline uint64_t mix64(uint64_t v)
+{
+	v ^= v >> 33; v *= 0xff51afd7ed558ccdULL; v ^= v >> 29; v *= 0xc4ceb9fe1a85ec53ULL; v ^= v >> 32;
+	return v;
+}
+
+static uint64_t digest_col(const col_t *c, uint64_t row_base, uint64_t val_base)
+{
+	uint64_t d = 0;
+	if (c->esz == 8) {
+		const uint64_t *p = c->p;
+		for (size_t i = 0; i < c->n; i++) d += mix64(p[i] + val_base) * (row_base + i + 1);
+	} else {
+		const uint32_t *p = c->p;
+		for (size_t i = 0; i < c->n; i++) d += mix64((uint64_t)(uint32_t)(p[i] + (uint32_t)val_base)) * (row_base + i + 1);
+	}
+	return d;
+}
+
+typedef struct {
+	const uint8_t *bytes; const zkb_sessions *sess; const zkb_xidtab *t;
+	uint32_t s0, s1;
+	zko_out o;
+	uint64_t base[4];      /* first FRAMES / STAT / BUF / ACL row of this thread's range */
+	uint64_t dig[29];
+} djob_t;
+
+static void *digest_decode_thread(void *arg)
+{
+	djob_t *j = arg;
+	out_init(&j->o, j->sess->nsessions);
+	decode_range(&j->o, j->bytes, j->sess, j->t, j->s0, j->s1, 0, 0);
+	return NULL;
+}
+
+static void *digest_fold_thread(void *arg)
+{
+	djob_t *j = arg;
+	zko_out *o = &j->o;
+	const col_t *cols[26] = { &o->frame_off, &o->frame_len, &o->session, &o->meta, &o->xid, &o->zxid,
+	    &o->err, &o->a0, &o->a1, &o->stat_frame, &o->czxid, &o->mzxid, &o->ctime, &o->mtime,
+	    &o->version, &o->cversion, &o->aversion, &o->ephemeralOwner, &o->dataLength,
+	    &o->numChildren, &o->pzxid, &o->buf_frame, &o->buf_off, &o->buf_len, &o->acl_frame,
+	    &o->acl_perms };
+	for (int c = 0; c < 26; c++) {
+		const int table = c < 9 ? 0 : c < 21 ? 1 : c < 24 ? 2 : 3;
+		/* the *_frame columns hold rows of this thread's own FRAMES table: shift to batch rows */
+		const uint64_t vb = (c == 9 || c == 21 || c == 24) ? j->base[0] : 0;
+		j->dig[c] = digest_col(cols[c], j->base[table], vb);
+	}
+	uint64_t d0 = 0, d1 = 0, d2 = 0;
+	for (uint32_t s = j->s0; s < j->s1; s++) {
+		d0 += mix64(o->sess_consumed[s]) * ((uint64_t)s + 1);
+		d1 += mix64(o->sess_bad_length_at[s]) * ((uint64_t)s + 1);
+		d2 += mix64((uint64_t)(uint32_t)(o->sess_first_frame[s] + (uint32_t)j->base[0])) * ((uint64_t)s + 1);
+	}
+	j->dig[26] = d0; j->dig[27] = d1; j->dig[28] = d2;
+	return NULL;
+}
+
+int zko_digest(const uint8_t *bytes, uint64_t nbytes, const zkb_sessions *sess, const zkb_xidtab *t,
+    int nthreads, uint64_t out_digest[29], uint64_t out_counts[4])
+{
+	int rc = check_sessions(nbytes, sess);
+	if (rc) return rc;
+	if (nthreads < 1) nthreads = 1;
+	if ((uint32_t)nthreads > sess->nsessions) nthreads = sess->nsessions ? (int)sess->nsessions : 1;
+	djob_t *jobs = calloc(nthreads, sizeof (djob_t));
+	pthread_t *th = calloc(nthreads, sizeof (pthread_t));
+	uint32_t s = 0;
+	for (int i = 0; i < nthreads; i++) {
+		uint64_t target = nbytes / nthreads * (i + 1);
+		uint32_t e = s;
+		if (i == nthreads - 1) e = sess->nsessions;
+		else while (e < sess->nsessions && sess->off[e + 1] <= target) e++;
+		if (e == s && s < sess->nsessions && i < nthreads - 1) e = s + 1;
+		jobs[i].bytes = bytes; jobs[i].sess = sess; jobs[i].t = t; jobs[i].s0 = s; jobs[i].s1 = e;
+		s = e;
+	}
+	for (int i = 0; i < nthreads; i++) pthread_create(&th[i], NULL, digest_decode_thread, &jobs[i]);
+	for (int i = 0; i < nthreads; i++) pthread_join(th[i], NULL);
+	uint64_t run[4] = { 0, 0, 0, 0 };
+	for (int i = 0; i < nthreads; i++) {
+		memcpy(jobs[i].base, run, sizeof (run));
+		run[0] += jobs[i].o.frame_off.n; run[1] += jobs[i].o.stat_frame.n;
+		run[2] += jobs[i].o.buf_frame.n; run[3] += jobs[i].o.acl_frame.n;
+	}
+	for (int i = 0; i < nthreads; i++) pthread_create(&th[i], NULL, digest_fold_thread, &jobs[i]);
+	for (int i = 0; i < nthreads; i++) pthread_join(th[i], NULL);
+	for (int c = 0; c < 29; c++) out_digest[c] = 0;
+	for (int i = 0; i < nthreads; i++) {
+		for (int c = 0; c < 29; c++) out_digest[c] += jobs[i].dig[c];
+		out_free(&jobs[i].o);
+	}
+	/* sess_first_frame has one more entry: [nsessions] = n_frames */
+	out_digest[28] += mix64((uint64_t)(uint32_t)run[0]) * ((uint64_t)sess->nsessions + 1);
+	memcpy(out_counts, run, sizeof (run));
+	free(jobs); free(th);
+	return 0;
+}
+
 /* ------------------------------------------------------------------------------ */
 /* xid map: zk-streams.js:145 — zcf_xidMap[pkt.xid] = pkt.opcode, last write wins  */
 

@@ -47,6 +47,9 @@ def load():
         lib.zko_bench_decode.argtypes = [P, C.c_uint64, C.POINTER(_abi.Sessions), C.POINTER(_abi.XidTab),
                                          C.c_int, C.c_uint64, C.c_int, C.POINTER(C.c_uint64),
                                          C.POINTER(C.c_uint64)]
+        lib.zko_digest.restype = C.c_int
+        lib.zko_digest.argtypes = [P, C.c_uint64, C.POINTER(_abi.Sessions), C.POINTER(_abi.XidTab), C.c_int,
+                                   C.POINTER(C.c_uint64 * 29), C.POINTER(C.c_uint64 * 4)]
         lib.zko_xidtab_build.restype = C.c_int
         lib.zko_xidtab_build.argtypes = [C.POINTER(_abi.Decoded), C.c_uint32, C.POINTER(_abi.XidTab), P]
         lib.zko_session_stats.restype = C.c_int
@@ -92,6 +95,49 @@ def bench_decode(data, sess_off, flags, handshake_frames, xidtab, mode, chunk, n
                                mode, chunk, nthreads, C.byref(frames), C.byref(chk))
     del keep
     return sec, frames.value
+
+
+DIGEST_COLUMNS = ([n for n, _ in _abi.FRAME_COLS + _abi.STAT_COLS + _abi.BUF_COLS + _abi.ACL_COLS] +
+                  [n for n, _ in _abi.SESS_COLS])
+
+
+def digest(data, sess_off, flags, handshake_frames, xidtab, nthreads):
+    """Whole-batch decode on `nthreads` threads folded into one order-sensitive 64-bit digest per
+    output column (zko_digest).  Returns ({column: digest}, (n_frames, n_stat, n_buf, n_acl))."""
+    lib = load()
+    buf = np.ascontiguousarray(data, dtype=np.uint8)
+    s, keep = _sessions(buf.size, sess_off, flags, handshake_frames)
+    xt = xidtab.struct() if xidtab is not None else None
+    dig, cnt = (C.c_uint64 * 29)(), (C.c_uint64 * 4)()
+    rc = lib.zko_digest(buf.ctypes.data if buf.size else None, buf.size, C.byref(s),
+                        C.byref(xt) if xt is not None else None, nthreads, C.byref(dig), C.byref(cnt))
+    if rc != 0:
+        raise ValueError("zko_digest failed: %d" % rc)
+    del keep
+    return dict(zip(DIGEST_COLUMNS, [int(x) for x in dig])), tuple(int(x) for x in cnt)
+
+
+def digest_columns(cols):
+    """The same digests computed from a Columns object (numpy), for the tests of zko_digest."""
+    M = (1 << 64) - 1
+
+    def mix(v):
+        v = v.astype(np.uint64)
+        v ^= v >> np.uint64(33); v *= np.uint64(0xff51afd7ed558ccd); v ^= v >> np.uint64(29)
+        v *= np.uint64(0xc4ceb9fe1a85ec53); v ^= v >> np.uint64(32)
+        return v
+
+    out = {}
+    for name in DIGEST_COLUMNS:
+        a = getattr(cols, name)
+        if a.dtype.itemsize == 4:
+            a = a.view(np.uint32)
+        else:
+            a = a.view(np.uint64)
+        w = np.arange(1, a.size + 1, dtype=np.uint64)
+        with np.errstate(over="ignore"):
+            out[name] = int((mix(a) * w).sum(dtype=np.uint64)) & M
+    return out
 
 
 def xidtab_build(req_cols, layout):

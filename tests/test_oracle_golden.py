@@ -163,3 +163,27 @@ def test_encode_then_decode_roundtrip(oracle, synth):
 def test_longdate():
     ld = LongDate(bytes.fromhex("0000014b3d2f9c00"))
     assert ld.toDate().year == 2015 and ld.toBuffer() == bytes.fromhex("0000014b3d2f9c00")
+
+
+def test_whole_batch_digest_matches_the_columns():
+    """zko_digest (threaded decode folded into one digest per column: bench.py's parity gate) and the
+    tensor-arithmetic digest the bench computes over the GPU's columns (verify.digest_tensor, run
+    here on CPU tensors) must both equal the digest of the oracle's own columns."""
+    import importlib
+    import torch
+    import zkoracle
+    synth = importlib.import_module("node-zkstream_b200.synth")
+    ver = importlib.import_module("node-zkstream_b200.verify")
+    for corpus in (synth.cfg2_mixed(5, 120, seed=3), synth.fuzz_corpus(5, nsessions=60, max_frames=30)):
+        d, off, fl, hs = corpus.arrays()
+        xt = corpus.xidtable()
+        cols = zkoracle.decode(d, off, fl, hs, xt)
+        want = zkoracle.digest_columns(cols)
+        for nt in (1, 4):
+            got, cnt = zkoracle.digest(d, off, fl, hs, xt, nt)
+            assert got == want
+            assert cnt == (cols.n_frames, cols.n_stat, cols.n_buf, cols.n_acl)
+        for name in ver.COLUMNS:
+            a = getattr(cols, name)
+            t = torch.from_numpy(a.view(np.int32 if a.dtype.itemsize == 4 else np.int64).copy())
+            assert ver.digest_tensor(t, a.size, chunk=257) == want[name], name
