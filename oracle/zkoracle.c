@@ -889,15 +889,15 @@ static void wb_buffer(wbuf_t *w, const uint8_t *arena, uint64_t off, int32_t len
 /* writeRequest and friends (zk-buffer.js:97-136,143-273,384-426), writeConnectRequest
  * (:32-39), writeConnectResponse (:50-56), wrapped by writeLengthPrefixed
  * (jute-buffer.js:181-189) as ZKEncodeStream._transform does (zk-streams.js:121-148). */
-int zko_encode(const zkb_requests *r, uint8_t **out, uint64_t *out_len, uint64_t *frame_off,
+static void encode_range(const zkb_requests *r, uint64_t lo, uint64_t hi, wbuf_t *wp, uint64_t *frame_off,
     uint8_t *status)
 {
-	wbuf_t w = { 0, 0, 0 };
-	for (uint64_t i = 0; i < r->n; i++) {
+	wbuf_t w = *wp;
+	for (uint64_t i = lo; i < hi; i++) {
 		uint64_t start = w.n;
 		int op = r->op[i];
 		int bad = 0;
-		frame_off[i] = start;
+		if (frame_off) frame_off[i] = start;
 		wb_int(&w, 0);   /* length back-patched below */
 		if (op == ZKB_ENC_CONNECT_REQUEST) {
 			wb_int(&w, r->a0[i]); wb_long(&w, r->zxid2[i]); wb_int(&w, r->a1[i]);
@@ -959,17 +959,67 @@ int zko_encode(const zkb_requests *r, uint8_t **out, uint64_t *out_len, uint64_t
 		}
 		if (bad) {
 			w.n = start;                       /* the reference throws: nothing is pushed */
-			status[i] = ZKB_ENC_UNSUPPORTED;
+			if (status) status[i] = ZKB_ENC_UNSUPPORTED;
 			continue;
 		}
-		status[i] = ZKB_ENC_OK;
+		if (status) status[i] = ZKB_ENC_OK;
 		uint32_t len = (uint32_t)(w.n - start - 4);
 		w.p[start] = (uint8_t)(len >> 24); w.p[start + 1] = (uint8_t)(len >> 16);
 		w.p[start + 2] = (uint8_t)(len >> 8); w.p[start + 3] = (uint8_t)len;
 	}
+	*wp = w;
+}
+
+int zko_encode(const zkb_requests *r, uint8_t **out, uint64_t *out_len, uint64_t *frame_off,
+    uint8_t *status)
+{
+	wbuf_t w = { 0, 0, 0 };
+	encode_range(r, 0, r->n, &w, frame_off, status);
 	frame_off[r->n] = w.n;
 	*out = w.p; *out_len = w.n;
 	return 0;
+}
+
+/* ---- timed CPU baseline of the encoder: packets sharded over threads, each thread grows its own
+ * output buffer as ZKEncodeStream's per-packet ZKBuffer would (zk-streams.js:121-148) ---------- */
+typedef struct { const zkb_requests *r; uint64_t lo, hi, bytes, chk; } ejob_t;
+
+static void *bench_encode_thread(void *arg)
+{
+	ejob_t *j = arg;
+	/* in groups of packets, so the frames stay cache sized as a socket writer would see them */
+	for (uint64_t lo = j->lo; lo < j->hi; lo += 65536) {
+		uint64_t hi = lo + 65536 < j->hi ? lo + 65536 : j->hi;
+		wbuf_t w = { 0, 0, 0 };
+		encode_range(j->r, lo, hi, &w, NULL, NULL);
+		j->bytes += w.n;
+		for (uint64_t k = 0; k < w.n; k += 64) j->chk += w.p[k];
+		free(w.p);
+	}
+	return NULL;
+}
+
+double zko_bench_encode(const zkb_requests *r, int nthreads, uint64_t *bytes, uint64_t *checksum)
+{
+	if (nthreads < 1) nthreads = 1;
+	ejob_t *jobs = calloc(nthreads, sizeof (ejob_t));
+	pthread_t *th = calloc(nthreads, sizeof (pthread_t));
+	for (int i = 0; i < nthreads; i++) {
+		jobs[i].r = r;
+		jobs[i].lo = r->n * (uint64_t)i / nthreads;
+		jobs[i].hi = r->n * (uint64_t)(i + 1) / nthreads;
+	}
+	struct timespec t0, t1;
+	clock_gettime(CLOCK_MONOTONIC, &t0);
+	for (int i = 0; i < nthreads; i++) pthread_create(&th[i], NULL, bench_encode_thread, &jobs[i]);
+	for (int i = 0; i < nthreads; i++) pthread_join(th[i], NULL);
+	clock_gettime(CLOCK_MONOTONIC, &t1);
+	uint64_t b = 0, c = 0;
+	for (int i = 0; i < nthreads; i++) { b += jobs[i].bytes; c += jobs[i].chk; }
+	if (bytes) *bytes = b;
+	if (checksum) *checksum = c;
+	free(jobs); free(th);
+	return (t1.tv_sec - t0.tv_sec) + (t1.tv_nsec - t0.tv_nsec) * 1e-9;
 }
 
 void zko_buf_free(uint8_t *p) { free(p); }

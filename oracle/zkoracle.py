@@ -58,6 +58,9 @@ def load():
         lib.zko_encode.restype = C.c_int
         lib.zko_encode.argtypes = [C.POINTER(_abi.Requests), C.POINTER(P), C.POINTER(C.c_uint64), P, P]
         lib.zko_buf_free.argtypes = [P]
+        lib.zko_bench_encode.restype = C.c_double
+        lib.zko_bench_encode.argtypes = [C.POINTER(_abi.Requests), C.c_int, C.POINTER(C.c_uint64),
+                                         C.POINTER(C.c_uint64)]
         _lib = lib
     return _lib
 
@@ -177,3 +180,13 @@ def encode(req):
     lib.zko_buf_free(out)
     del keep
     return data, fo, st[:req.n]
+
+
+def bench_encode(req, nthreads):
+    """Timed multi-thread CPU encode of a RequestBatch; returns (seconds, frame bytes written)."""
+    lib = load()
+    r, keep = req.struct()
+    nb, chk = C.c_uint64(), C.c_uint64()
+    sec = lib.zko_bench_encode(C.byref(r), nthreads, C.byref(nb), C.byref(chk))
+    del keep
+    return sec, nb.value
