@@ -27,6 +27,8 @@
  *                   over per-chunk row counts, so the input is read from HBM once and the side
  *                   tables come out dense and ordered.
  */
+#include <stdlib.h>
+
 #include "zk_internal.h"
 
 namespace {
@@ -89,27 +91,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 	    "bra ZK_WAIT_%=;\n"
 	    "ZK_DONE_%=:\n"
 	    "}\n" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-
-/* look-back descriptors: one 128-bit relaxed gpu-scope access each way (never cached in
- * L1, never hoisted out of the polling loop) */
-__device__ __forceinline__ uint4 ld_desc(const uint4 *p)
-{
-	uint4 r;
-	asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-	    : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
-	return r;
-}
-__device__ __forceinline__ uint32_t ld_state(const uint4 *p)
-{
-	uint32_t r;
-	asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
-	return r;
-}
-__device__ __forceinline__ void st_desc(uint4 *p, uint4 v)
-{
-	asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};"
-	    :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 /* ================================================================================== */
@@ -825,6 +806,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const 
 	if (g == a.n_gran - 1) a.ctrl->n_frames = (unsigned long long)ex.c + x.c;
 }
 
+/* between the first scan of a split and its fix-up round: keep what the scan counted, start afresh */
+__global__ void k_split_round(zk_ctrl *ctrl)
+{
+	ctrl->first_dirty[0] = ctrl->n_dirty; ctrl->first_dirty[1] = ctrl->n_rewalk;
+	ctrl->n_dirty = 0; ctrl->n_rewalk = 0;
+}
+
 /* checks off[0] == 0, off[n] == nbytes, monotone */
 __global__ void k_check_sessions(const uint64_t *off, const uint8_t *flags, uint32_t nsess, uint64_t nbytes,
     zk_ctrl *ctrl)
@@ -877,8 +865,10 @@ struct DecArgs {
 	uint32_t        n_chunks;
 	uint64_t        n_frames;
 	zkb_decoded     o;
-	uint4          *lb;           /* [n_chunks] { state, stat rows, buf rows, acl rows } */
-	uint32_t        chunk0;       /* first chunk of this launch (a look-back pass may redo only the tail of a batch) */
+	uint4          *c_rows;       /* [n_chunks] { needs the exact body, stat rows, buf rows, acl rows } the chunk really has */
+	uint4          *c_base;       /* [n_chunks] exclusive prefix of c_rows (redo passes) */
+	uint32_t        chunk0;       /* first chunk of this launch (a redo covers only the tail of a batch) */
+	uint32_t        force_exact;  /* every chunk takes the exact body (prediction switched off) */
 	zk_ctrl        *ctrl;
 };
 
@@ -1013,12 +1003,26 @@ enum { VEC_NONE = 0, VEC_STR1 = 1, VEC_ACL = 2, VEC_STR3 = 3 };
 #define ZK_BMW         (ZK_SLOTS / 32)
 #define ZK_DEC_WARPS   4
 
+/* deferred vector walk of the direct body: one entry per frame whose vector is walked later */
+struct VEnt { uint32_t w0, w1, w2, w3; };   /* pr | vrel << 16;  buf row | acl row << 16 (chunk relative);  stat row | kind << 16;  frame index in chunk */
+#define ZK_VL_CAP   64u
+#define ZK_BM_BYTES (6u * ZK_BMW * 4u + (ZK_BMW + 2u) * 2u)
+#define ZK_FREL_CAP ((ZK_BM_BYTES - ZK_VL_CAP * 16u) / 2u)
+
 struct __align__(16) ChunkSm {
 	uint8_t  tile[ZK_WIN + 16];
-	uint32_t m_buf[ZK_BMW], m_acl[ZK_BMW], m_stat[ZK_BMW];
-	uint32_t sub0[ZK_BMW], sub1[ZK_BMW];
-	uint32_t fstart[ZK_BMW];       /* slots where a frame's length prefix starts */
-	uint16_t fpre[ZK_BMW + 2];     /* exclusive prefix of popc(fstart[w]) */
+	union {
+		struct {      /* exact body: one bit per 4-byte slot */
+			uint32_t m_buf[ZK_BMW], m_acl[ZK_BMW], m_stat[ZK_BMW];
+			uint32_t sub0[ZK_BMW], sub1[ZK_BMW];
+			uint32_t fstart[ZK_BMW];       /* slots where a frame's length prefix starts */
+			uint16_t fpre[ZK_BMW + 2];     /* exclusive prefix of popc(fstart[w]) */
+		};
+		struct {      /* direct body */
+			VEnt     vl[ZK_VL_CAP];        /* frames whose vector is still to be walked */
+			uint16_t frel[ZK_FREL_CAP];    /* tile offset of frame (window start + i) */
+		};
+	};
 };
 
 enum { WALK_COUNT = 0, WALK_EMIT = 1, WALK_MARK = 2 };
@@ -1637,8 +1641,9 @@ __device__ unsigned long long zk_hist[3][64];
 
 /* Everything one warp does for one 8 KiB chunk.  `phase` is the parity of the warp's
  * mbarrier for this use (it flips every chunk). */
-template <bool PRED, int DIR>
-__device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
+enum { XM_COUNT = 0, XM_EMIT = 1 };
+template <int XM, int DIR>
+__device__ __forceinline__ void decode_chunk_exact(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
     const uint32_t chunk, const uint32_t lane, const long long zk_t0)
 {
 #ifdef ZK_PROFILE_PHASES
@@ -1911,90 +1916,19 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 	const uint32_t tb = nb + warp_sum(lp.n_buf), ta = na + warp_sum(lp.n_acl), ts = ns + warp_sum(lp.n_stat);
 	__syncwarp();
 
-	/* ---- decoupled look-back over chunks: exclusive prefix of (stat, buf, acl) rows.
-	 * A chunk's descriptor is one aligned 16-byte word { state, stat, buf, acl } written and
-	 * read with single 128-bit accesses, so state and counts always belong together: first
-	 * the chunk's own totals (AGG), later its inclusive prefix (PFX). ---- */
+	/* ---- where the chunk's rows go.  The exact body never guesses: a first launch (XM_COUNT) only
+	 * publishes what the chunk really has, a scan over all chunks turns that into every chunk's
+	 * first rows, and a second launch (XM_EMIT) parses again and places them.  No chunk ever waits
+	 * for another. ---- */
 	ZK_T(5);
-	uint32_t e0 = 0, e1 = 0, e2 = 0;
-	if (PRED) {
-		/* The splitter predicted this chunk's rows (predict_rows): they start at rb0 if every
-		 * chunk really has what was predicted for it.  One that does not raises the flag; the
-		 * host then repeats the pass with the look-back, and this pass's rows do not matter. */
-		const uint4 rb0 = a.g_rbase[g0], rb1 = a.g_rbase[g1 < a.n_gran ? g1 : a.n_gran];
-		e0 = rb0.x; e1 = rb0.y; e2 = rb0.z;
-		if (ts != rb1.x - rb0.x || tb != rb1.y - rb0.y || ta != rb1.z - rb0.z) {
-			if (lane == 0) { atomicOr(&a.ctrl->error, ZK_DERR_MISPREDICT); atomicMin(&a.ctrl->first_bad, chunk); }
-			return;
-		}
-	} else if (chunk == a.chunk0) {
-		/* a pass that redoes the tail of a batch starts from the predicted rows of its first
-		 * chunk: every chunk before it matched its prediction, so they are the real ones */
-		if (a.chunk0) { const uint4 seed = a.g_rbase[g0]; e0 = seed.x; e1 = seed.y; e2 = seed.z; }
-	} else {
-		uint4 seed = make_uint4(ZK_LB_PFX, 0, 0, 0);
-		if (a.chunk0) {
-			const uint4 rb = a.g_rbase[a.chunk0 << gsh];
-			seed.y = rb.x; seed.z = rb.y; seed.w = rb.z;
-		}
-		if (lane == 0) st_desc(a.lb + chunk, make_uint4(ZK_LB_AGG, ts, tb, ta));
-		/* Each round looks at the 128 chunks before position j: lane l reads chunks j-l,
-		 * j-32-l, j-64-l, j-96-l with four independent loads (one round trip).  It can finish
-		 * as soon as the nearest full prefix has no unpublished chunk in front of it. */
-		int64_t j = (int64_t)chunk - 1;
-		uint32_t spins = 0, ns_sleep = ZK_SLEEP_MIN;
-		for (;;) {
-			uint4 d[4];
-#pragma unroll
-			for (int q = 0; q < 4; ++q) {
-				const int64_t idx = j - 32 * q - (int64_t)lane;
-				d[q] = seed;                         /* everything before the launch's first chunk */
-				if (idx >= (int64_t)a.chunk0) d[q] = ld_desc(a.lb + idx);
-			}
-			bool done = false, wait = false;
-			int64_t hole_idx = 0;
-			uint32_t s0 = 0, s1 = 0, s2 = 0;
-#pragma unroll
-			for (int q = 0; q < 4; ++q) {
-				if (done || wait) continue;
-				const uint32_t pm = __ballot_sync(0xffffffffu, d[q].x == ZK_LB_PFX);
-				const uint32_t em = __ballot_sync(0xffffffffu, d[q].x == ZK_LB_EMPTY);
-				const int first = __ffs(pm) - 1;       /* nearest full prefix in this group */
-				const int hole = __ffs(em) - 1;        /* nearest chunk that has published nothing */
-				if (hole >= 0 && (first < 0 || hole < first)) { wait = true; hole_idx = j - 32 * q - hole; continue; }
-				const bool use = (first < 0 || (int)lane <= first);
-				s0 += use ? d[q].y : 0u; s1 += use ? d[q].z : 0u; s2 += use ? d[q].w : 0u;
-				if (first >= 0) done = true;
-			}
-			if (wait) {
-				/* Wait on that one chunk (a single word, the same address for the whole warp)
-				 * instead of re-reading the window: a spinning warp takes issue slots from the
-				 * warps still parsing, so the poll is kept to a handful of instructions. */
-				bool gave_up = false;
-				for (;;) {
-					if (++spins > ZK_SPIN_LIMIT) { gave_up = true; break; }
-					__nanosleep(ns_sleep);
-					if (ns_sleep < ZK_SLEEP_MAX) ns_sleep <<= 1;
-					if (ld_state(a.lb + hole_idx) != ZK_LB_EMPTY) break;
-				}
-				if (gave_up) {
-					if (lane == 0) atomicOr(&a.ctrl->error, ZK_DERR_LOOKBACK);
-					break;
-				}
-				continue;
-			}
-			e0 += warp_sum(s0); e1 += warp_sum(s1); e2 += warp_sum(s2);
-			if (done) break;
-			j -= 128;
-		}
+	if (XM == XM_COUNT) {
+		if (lane == 0) a.c_rows[chunk] = make_uint4(1u, ts, tb, ta);
+		return;
 	}
-	if (lane == 0) {
-		if (!PRED) st_desc(a.lb + chunk, make_uint4(ZK_LB_PFX, e0 + ts, e1 + tb, e2 + ta));
-		if (chunk == a.n_chunks - 1) {
-			a.ctrl->n_stat = (unsigned long long)e0 + ts;
-			a.ctrl->n_buf = (unsigned long long)e1 + tb;
-			a.ctrl->n_acl = (unsigned long long)e2 + ta;
-		}
+	uint32_t e0, e1, e2;
+	{
+		const uint4 cb = a.c_base[chunk];
+		e0 = cb.y; e1 = cb.z; e2 = cb.w;
 	}
 	ZK_T(6);
 	ZK_ACC(0, zk_t0, zk_t1); ZK_ACC(1, zk_t1, zk_t2); ZK_ACC(2, zk_t2, zk_t3); ZK_ACC(3, zk_t3, zk_t4);
@@ -2104,18 +2038,34 @@ __device__ __forceinline__ void decode_chunk(const DecArgs &a, ChunkSm &c, uint6
 #endif
 }
 
-/* One CTA = ZK_DEC_WARPS warps = that many consecutive chunks, chunk index from blockIdx.
- * The look-back only ever waits for chunks of lower-numbered CTAs; like CUB's single-pass
- * scan this relies on the hardware starting CTAs in index order (it does), and the spin
- * limit in the look-back turns any violation into an error instead of a hang.  (Measured
- * alternatives — an atomic ticket per warp or per CTA, persistent warps looping over
- * tickets, 4 KiB chunks at higher occupancy — were all slower: profiles/r1_notes.md.)
- * The warps of a CTA never wait for each other. */
+#include "zk_decode_direct.cuh"
+
+/* One CTA = ZK_DEC_WARPS warps = that many consecutive chunks, chunk index from blockIdx.  The
+ * warps of a CTA never wait for each other, and no chunk ever waits for another chunk.
+ *   k_decode<DIR, false>   the ordinary pass: direct placement from the splitter's predicted rows
+ *   k_decode<DIR, true>    the same body placing from scanned real counts (after a misprediction)
+ *   k_decode_exact<DIR, XM_COUNT / XM_EMIT>   the exact body, for the chunks that need it
+ * DIR: 1 = every session of the batch is client->server, 2 = every one is server->client, 0 = mixed. */
 #ifndef ZK_DEC_MINBLOCKS
 #define ZK_DEC_MINBLOCKS 5
 #endif
-template <bool PRED, int DIR>
+template <int DIR, bool REDO>
 __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(DecArgs a)
+{
+	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
+	__shared__ __align__(8) uint64_t s_bar[ZK_DEC_WARPS];
+	const uint32_t lane = threadIdx.x & 31;
+	ChunkSm &c = sm_all[threadIdx.x >> 5];
+	uint64_t *bar = &s_bar[threadIdx.x >> 5];
+	const uint32_t chunk = a.chunk0 + blockIdx.x * ZK_DEC_WARPS + (threadIdx.x >> 5);
+	if (chunk >= a.n_chunks) return;
+	if (lane == 0) mbar_init(bar, 1);
+	__syncwarp();
+	decode_chunk_direct<DIR, REDO>(a, c, bar, chunk, lane);
+}
+
+template <int DIR, int XM>
+__global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode_exact(DecArgs a)
 {
 	__shared__ __align__(16) ChunkSm sm_all[ZK_DEC_WARPS];
 	__shared__ __align__(8) uint64_t s_bar[ZK_DEC_WARPS];
@@ -2129,9 +2079,47 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode(
 #endif
 	const uint32_t chunk = a.chunk0 + blockIdx.x * ZK_DEC_WARPS + (threadIdx.x >> 5);
 	if (chunk >= a.n_chunks) return;
+	if (!a.force_exact && !a.c_rows[chunk].x) return;      /* the direct body has this chunk */
 	if (lane == 0) mbar_init(bar, 1);
 	__syncwarp();
-	decode_chunk<PRED, DIR>(a, c, bar, 0, chunk, lane, t0);
+	decode_chunk_exact<XM, DIR>(a, c, bar, 0, chunk, lane, t0);
+}
+
+/* Exclusive prefix of the chunks' real row counts from chunk0 on, seeded with the rows before
+ * chunk0 (all of which are where they belong); the totals go to the control block.  One block:
+ * this only runs after a misprediction, or with the prediction switched off. */
+__global__ void __launch_bounds__(1024) k_rows_scan(const uint4 *rows, uint4 *base, uint32_t chunk0, uint32_t n_chunks,
+    uint4 seed, zk_ctrl *ctrl)
+{
+	__shared__ uint32_t s_tot[3][1024];
+	const uint32_t n = n_chunks - chunk0;
+	const uint32_t per = (n + 1023u) / 1024u;
+	const uint32_t lo = chunk0 + threadIdx.x * per;
+	const uint32_t hi = (lo + per < n_chunks) ? lo + per : n_chunks;
+	uint32_t x0 = 0, x1 = 0, x2 = 0;
+	for (uint32_t i = lo; i < hi; ++i) { const uint4 r = rows[i]; x0 += r.y; x1 += r.z; x2 += r.w; }
+	s_tot[0][threadIdx.x] = x0; s_tot[1][threadIdx.x] = x1; s_tot[2][threadIdx.x] = x2;
+	__syncthreads();
+	/* Hillis-Steele over the 1024 partial sums */
+	for (uint32_t d = 1; d < 1024; d <<= 1) {
+		uint32_t y0 = 0, y1 = 0, y2 = 0;
+		if (threadIdx.x >= d) { y0 = s_tot[0][threadIdx.x - d]; y1 = s_tot[1][threadIdx.x - d]; y2 = s_tot[2][threadIdx.x - d]; }
+		__syncthreads();
+		s_tot[0][threadIdx.x] += y0; s_tot[1][threadIdx.x] += y1; s_tot[2][threadIdx.x] += y2;
+		__syncthreads();
+	}
+	uint32_t b0 = seed.x + s_tot[0][threadIdx.x] - x0, b1 = seed.y + s_tot[1][threadIdx.x] - x1,
+	    b2 = seed.z + s_tot[2][threadIdx.x] - x2;
+	for (uint32_t i = lo; i < hi; ++i) {
+		const uint4 r = rows[i];
+		base[i] = make_uint4(0, b0, b1, b2);
+		b0 += r.y; b1 += r.z; b2 += r.w;
+	}
+	if (threadIdx.x == 1023) {
+		ctrl->n_stat = (unsigned long long)seed.x + s_tot[0][1023];
+		ctrl->n_buf = (unsigned long long)seed.y + s_tot[1][1023];
+		ctrl->n_acl = (unsigned long long)seed.z + s_tot[2][1023];
+	}
 }
 
 /* ================================================================================== */
@@ -2173,7 +2161,11 @@ __global__ void k_xid_finish(const unsigned long long *tmp, uint64_t n, int8_t *
 
 static uint32_t zk_pick_glog2(uint64_t nbytes)
 {
-	/* aim for ~256K granules so the splitter has enough threads, within [1 KiB, 32 KiB] */
+	/* development knob: ZKBATCH_GLOG2=11..13 fixes the granule size */
+	static int forced = -1;
+	if (forced < 0) { const char *e = getenv("ZKBATCH_GLOG2"); forced = e ? atoi(e) : 0; }
+	if (forced >= ZK_GRAN_MIN_LOG2 && forced <= ZK_GRAN_MAX_LOG2 && forced <= (int)ZK_CHUNK_LOG2) return (uint32_t)forced;
+	/* aim for ~256K granules so the splitter has enough threads, within [2 KiB, 8 KiB] */
 	uint64_t want = (nbytes + 262143) / 262144;
 	uint32_t l = ZK_GRAN_MIN_LOG2;
 	while (l < ZK_GRAN_MAX_LOG2 && l < ZK_CHUNK_LOG2 && (1ull << l) < want) l++;
@@ -2181,7 +2173,7 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 }
 
 struct ScratchLayout {
-	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, lb, total;
+	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, c_rows, c_base, total;
 	uint32_t glog2, n_gran, n_chunks, n_blk;
 };
 
@@ -2209,7 +2201,8 @@ static ScratchLayout zk_layout(uint64_t nbytes)
 	L.g_rows = o;    o += zk_align_up((size_t)L.n_gran * 2 * 16, 256);
 	L.g_rbase = o;   o += zk_align_up((size_t)(L.n_gran + 1) * 16, 256);
 	L.blk = o;       o += zk_align_up((size_t)(L.n_blk + 1) * sizeof (ScanVal), 256);
-	L.lb = o;        o += zk_align_up((size_t)L.n_chunks * 16, 256);
+	L.c_rows = o;    o += zk_align_up((size_t)L.n_chunks * 16, 256);
+	L.c_base = o;    o += zk_align_up((size_t)L.n_chunks * 16, 256);
 	L.total = o;
 	return L;
 }
@@ -2295,6 +2288,8 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	ZK_EV(ctx, 0);
 	k_split<MODE_SPEC><<<split_blocks, 128, 0, ctx->stream>>>(sa);
 	LAUNCH_CHECK(ctx);
+	/* Ordinary traffic needs exactly one fix-up round, so SPEC, scan, FIX, scan are queued back to back
+	 * and the host looks at the result once; FIX returns at once in granules that are not dirty. */
 	for (uint32_t iter = 0;; ++iter) {
 		k_scan_reduce<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk);
 		LAUNCH_CHECK(ctx);
@@ -2302,11 +2297,23 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 		LAUNCH_CHECK(ctx);
 		k_scan_apply<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk);
 		LAUNCH_CHECK(ctx);
+		if (iter == 0) {
+			k_split_round<<<1, 1, 0, ctx->stream>>>(ctx->d_ctrl);
+			LAUNCH_CHECK(ctx);
+			k_split<MODE_FIX><<<split_blocks, 128, 0, ctx->stream>>>(sa);
+			LAUNCH_CHECK(ctx);
+			continue;
+		}
 		ZK_EV(ctx, 1);
 		if ((rc = zk_read_ctrl(ctx))) return rc;
 		if (ctx->h_ctrl->error & ZK_DERR_SESSIONS) {
 			snprintf(ctx->err, sizeof (ctx->err), "zkb_decode: session offsets invalid");
 			return ZKB_EINVAL;
+		}
+		if (iter == 1) {
+			ctx->split_iters[0][0] = ctx->h_ctrl->first_dirty[0];
+			ctx->split_iters[0][1] = ctx->h_ctrl->first_dirty[1];
+			if (ctx->h_ctrl->first_dirty[0]) ctx->split_fixups++;
 		}
 		if (iter < 32) {
 			ctx->split_iters[iter][0] = ctx->h_ctrl->n_dirty;
@@ -2383,41 +2390,75 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	da.g_openlocal = sa.g_openlocal; da.g_sub = sa.g_sub; da.g_sel = sa.g_sel;
 	da.glog2 = L.glog2; da.n_gran = L.n_gran; da.n_chunks = L.n_chunks;
 	da.n_frames = n_frames; da.o = *out;
-	da.lb = (uint4 *)(S + L.lb); da.ctrl = ctx->d_ctrl;
+	da.c_rows = (uint4 *)(S + L.c_rows); da.c_base = (uint4 *)(S + L.c_base); da.ctrl = ctx->d_ctrl;
 	da.g_rbase = sa.g_rbase;
 	const unsigned dec_blocks = (L.n_chunks + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS;
+	const unsigned dec_threads = ZK_DEC_WARPS * 32;
 	ZK_EV(ctx, 4);
-	bool lookback = ctx->no_predict != 0;
+	bool redo = ctx->no_predict != 0;
 	unsigned long long slow_first = 0;
 	bool have_slow = false;
-	if (!lookback) {
-		/* first try: every chunk places its rows where the splitter predicted */
+	if (!redo) {
+		/* the ordinary pass: every chunk places its rows where the splitter predicted */
 		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->first_bad, 0xFF, sizeof (unsigned int), ctx->stream));
-		if (ctx->dir == 1) k_decode<true, 1><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
-		else if (ctx->dir == 2) k_decode<true, 2><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
-		else k_decode<true, 0><<<dec_blocks, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		if (ctx->dir == 1) k_decode<1, false><<<dec_blocks, dec_threads, 0, ctx->stream>>>(da);
+		else if (ctx->dir == 2) k_decode<2, false><<<dec_blocks, dec_threads, 0, ctx->stream>>>(da);
+		else k_decode<0, false><<<dec_blocks, dec_threads, 0, ctx->stream>>>(da);
 		LAUNCH_CHECK(ctx);
 		if ((rc = zk_read_ctrl(ctx))) return rc;
 		if (ctx->h_ctrl->error == ZK_DERR_MISPREDICT) {
 			/* Some frame is not what its header promised.  Every chunk before the first one that
 			 * noticed has its rows in the right place (its own and all earlier counts matched);
-			 * the rest of the batch is done again, rows placed by look-back from there on. */
+			 * the rest of the batch is placed again from the chunks' real counts. */
 			ctx->mispredicts++;
-			lookback = true;
+			redo = true;
 			da.chunk0 = ctx->h_ctrl->first_bad < L.n_chunks ? ctx->h_ctrl->first_bad : 0;
 			slow_first = ctx->h_ctrl->n_slow;      /* the first pass already saw every frame */
 			have_slow = true;
 			ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->error, 0, sizeof (unsigned int), ctx->stream));
+		} else {
+			/* the prediction held: its totals are the real ones */
+			ctx->h_ctrl->n_stat = ctx->pred_rows[0]; ctx->h_ctrl->n_buf = ctx->pred_rows[1];
+			ctx->h_ctrl->n_acl = ctx->pred_rows[2];
 		}
 	}
-	if (lookback) {
+	if (redo) {
+		/* exact route, no chunk waits for another: (1) the chunks the direct body could not vouch for
+		 * (all of them when the prediction is switched off) count their rows with the exact body,
+		 * (2) one scan turns every chunk's real counts into its first rows, (3) the direct body places
+		 * the sound chunks again, the exact body the others. */
 		const uint32_t todo = L.n_chunks - da.chunk0;
-		ZK_CUDA(ctx, cudaMemsetAsync(da.lb + da.chunk0, 0, (size_t)todo * 16, ctx->stream));
-		k_decode<false, 0><<<(todo + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS, ZK_DEC_WARPS * 32, 0, ctx->stream>>>(da);
+		const unsigned blocks = (todo + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS;
+		da.force_exact = ctx->no_predict ? 1u : 0u;
+		uint4 seed = make_uint4(0, 0, 0, 0);
+		if (da.chunk0) {
+			uint4 rb;
+			ZK_CUDA(ctx, cudaMemcpyAsync(&rb, sa.g_rbase + ((size_t)da.chunk0 << (ZK_CHUNK_LOG2 - L.glog2)), sizeof (rb),
+			    cudaMemcpyDeviceToHost, ctx->stream));
+			ZK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+			seed = rb;
+		}
+#define ZK_LAUNCH_EXACT(XM)                                                                              \
+		do {                                                                                             \
+			if (ctx->dir == 1) k_decode_exact<1, XM><<<blocks, dec_threads, 0, ctx->stream>>>(da);       \
+			else if (ctx->dir == 2) k_decode_exact<2, XM><<<blocks, dec_threads, 0, ctx->stream>>>(da);  \
+			else k_decode_exact<0, XM><<<blocks, dec_threads, 0, ctx->stream>>>(da);                     \
+			LAUNCH_CHECK(ctx);                                                                           \
+		} while (0)
+		ZK_LAUNCH_EXACT(XM_COUNT);
+		k_rows_scan<<<1, 1024, 0, ctx->stream>>>(da.c_rows, da.c_base, da.chunk0, L.n_chunks, seed, ctx->d_ctrl);
 		LAUNCH_CHECK(ctx);
+		if (!da.force_exact) {
+			if (ctx->dir == 1) k_decode<1, true><<<blocks, dec_threads, 0, ctx->stream>>>(da);
+			else if (ctx->dir == 2) k_decode<2, true><<<blocks, dec_threads, 0, ctx->stream>>>(da);
+			else k_decode<0, true><<<blocks, dec_threads, 0, ctx->stream>>>(da);
+			LAUNCH_CHECK(ctx);
+		}
+		ZK_LAUNCH_EXACT(XM_EMIT);
+#undef ZK_LAUNCH_EXACT
 	}
 	ZK_EV(ctx, 5);
-	if (lookback && (rc = zk_read_ctrl(ctx))) return rc;
+	if (redo && (rc = zk_read_ctrl(ctx))) return rc;
 	if (have_slow) ctx->h_ctrl->n_slow = slow_first;
 	if (ctx->timing) ZK_CUDA(ctx, cudaEventSynchronize(ctx->ev[5]));
 	if (ctx->timing) {

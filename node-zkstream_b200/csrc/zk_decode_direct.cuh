@@ -1,0 +1,546 @@
+/*
+ * zk_decode_direct.cuh — the decode kernel's ordinary body ("direct placement"); included by
+ * zk_decode.cu inside its anonymous namespace, after the readers it shares with the exact body.
+ *
+ * One warp per 8 KiB chunk, as in the exact body, but nothing is recorded in bitmaps and nothing is
+ * compacted afterwards: every side-table row is written where it belongs the moment its field is
+ * read.  That is possible because
+ *   - the chunk's first STAT / BUF / ACL rows are known before the kernel starts (the splitter's
+ *     walk counted the rows each frame header promises, its scan carried the sums), and
+ *   - inside the chunk the same header arithmetic gives every frame's row counts before any of its
+ *     rows is written, so one warp scan per round of 32 frames turns them into each frame's first rows.
+ * Frame headers and fixed fields are read by the frame's own lane in a few converged stages (path,
+ * data, tail) instead of one branch per opcode; vectors (children, ACLs) are set aside and walked
+ * together, one lane per vector frame, once enough have gathered or the chunk is done.
+ *
+ * What the header promised is verified as the fields are read.  A frame that breaks the promise (its
+ * vector runs out of bytes) leaves rows it reserved unwritten: the chunk is flagged, and the host
+ * runs the exact two-launch route from that chunk on (zk_fields_device).  A chunk whose total differs
+ * from the splitter's prediction only raises the batch-wide flag: its rows are right relative to
+ * each other and are placed again from the scanned bases.
+ */
+
+enum { VK_STR = 1, VK_STR_STAT = 2, VK_ACL_STAT = 3, VK_ACL_FLAGS = 4 };
+
+/* The loop of ZKDecodeStream._transform (zk-streams.js:47-64) over one lane's 256-byte sub-range of
+ * the staged chunk, from where the splitter says the chain stands there.
+ * STORE == false: count the frames that start in the sub-range.
+ * STORE == true:  store the tile offset of the lane's frames with chunk-local index in
+ *                 [wlo, wlo + ZK_FREL_CAP) into c.frel; if `book`, also write consumed /
+ *                 bad_length_at of sessions that end here and first_frame of sessions that start here
+ *                 (`fbase` = batch row of the lane's first frame). */
+template <bool STORE>
+__device__ __forceinline__ uint32_t walk_subrange(const DecArgs &a, ChunkSm &c, const uint64_t cs, const uint64_t hi,
+    const uint64_t entry, uint32_t s, uint64_t send, const uint32_t wlo, const uint32_t lbase, const bool book,
+    const uint32_t fbase, const bool entry_is_start)
+{
+	uint32_t cnt = 0;
+	if (entry == ZK_NONE) return 0;
+	uint64_t pos = entry;
+	if (STORE && book && entry_is_start) a.o.sess_first_frame[s] = fbase;
+	for (;;) {
+		uint64_t bad = ZK_NONE;
+		bool stop = false;
+		for (;;) {
+			if (pos == send) { stop = true; break; }
+			if (pos >= hi) break;
+			const uint64_t rem = send - pos;
+			if (rem < 4) { stop = true; break; }                      /* zd_used < 4 */
+			const uint32_t rel = (uint32_t)(pos - cs);
+			const int32_t len = (int32_t)sm_be32(c.tile, rel);
+			if (!len_ok(len)) { stop = true; bad = pos; break; }      /* :49-53 BAD_LENGTH */
+			if (rem < 4 + (uint64_t)len) { stop = true; break; }      /* frame not complete yet */
+			if (STORE) {
+				const uint32_t i = lbase + cnt - wlo;
+				if (i < ZK_FREL_CAP) c.frel[i] = (uint16_t)rel;
+			}
+			cnt++;
+			pos += 4 + (uint64_t)len;
+		}
+		if (!stop) break;                 /* the chain leaves the sub-range alive */
+		if (STORE && book) {
+			a.o.sess_consumed[s] = pos;
+			a.o.sess_bad_length_at[s] = bad;
+		}
+		/* next session, if it starts inside this sub-range */
+		if (s + 1 >= a.nsess) break;
+		const uint64_t so = send;
+		if (!(so < hi)) break;
+		s++;
+		pos = so;
+		send = __ldg(a.sess_off + s + 1);
+		if (STORE && book) a.o.sess_first_frame[s] = fbase + cnt;
+	}
+	return cnt;
+}
+
+/* one BUF row */
+__device__ __forceinline__ void put_buf(const zkb_decoded &o, uint32_t row, uint32_t frame, uint64_t off, int32_t len)
+{
+	if (row < o.cap_buf) {
+		o.buf_frame[row] = frame;
+		o.buf_off[row] = off;
+		o.buf_len[row] = len;
+	}
+}
+
+/* one STAT row from the 68 bytes at tile offset q (readStat, zk-buffer.js:428-442) */
+__device__ __forceinline__ void put_stat(const zkb_decoded &o, const uint8_t *tile, uint32_t q, uint32_t row, uint32_t frame)
+{
+	if (row >= o.cap_stat) return;
+	/* 68 bytes = 17 big-endian words from 18 aligned shared-memory words */
+	const uint32_t *wp = reinterpret_cast<const uint32_t *>(tile + (q & ~3u));
+	const uint32_t sh = (q & 3u) * 8;
+	uint32_t x[18];
+#pragma unroll
+	for (int i = 0; i < 18; ++i) x[i] = wp[i];
+	uint32_t v[17];
+#pragma unroll
+	for (int i = 0; i < 17; ++i) v[i] = bswap32(__funnelshift_r(x[i], x[i + 1], sh));
+#define Q64(i) ((int64_t)(((uint64_t)v[i] << 32) | (uint64_t)v[(i) + 1]))
+	o.stat_frame[row] = frame;
+	o.czxid[row] = Q64(0); o.mzxid[row] = Q64(2); o.ctime[row] = Q64(4); o.mtime[row] = Q64(6);
+	o.version[row] = (int32_t)v[8]; o.cversion[row] = (int32_t)v[9]; o.aversion[row] = (int32_t)v[10];
+	o.ephemeralOwner[row] = Q64(11);
+	o.dataLength[row] = (int32_t)v[13]; o.numChildren[row] = (int32_t)v[14];
+	o.pzxid[row] = Q64(15);
+#undef Q64
+}
+
+/* Walk the vectors set aside so far, one lane per frame.  Returns false in a lane whose frame did
+ * not keep what its header promised. */
+__device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, const uint64_t cs, const uint32_t f0,
+    const uint32_t e0, const uint32_t e1, const uint32_t e2, const uint32_t nv, const uint32_t lane)
+{
+	const zkb_decoded &o = a.o;
+	bool good = true;
+	for (uint32_t i = lane; i < nv; i += 32) {
+		const VEnt e = c.vl[i];
+		const uint32_t pr = e.w0 & 0xffffu, vrel = e.w0 >> 16;
+		uint32_t brow = e1 + (e.w1 & 0xffffu), arow = e2 + (e.w1 >> 16);
+		const uint32_t srow = e0 + (e.w2 & 0xffffu), kind = e.w2 >> 16;
+		const uint32_t frame = f0 + e.w3;
+		const uint32_t end = pr + sm_be32(c.tile, pr - 4);          /* tile offset one past the payload */
+		const int32_t count = (int32_t)sm_be32(c.tile, vrel);
+		uint32_t cur = vrel + 4;
+		bool ok = true;
+		if (kind == VK_STR || kind == VK_STR_STAT) {
+			/* vector<ustring> (zk-buffer.js:334-337) */
+			for (int32_t k = 0; k < count; ++k) {
+				if (cur + 4 > end) { ok = false; break; }
+				const int32_t l = (int32_t)sm_be32(c.tile, cur);
+				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+				if (cur + 4 + ul > end) { ok = false; break; }
+				put_buf(o, brow++, frame, cs + cur + 4, (int32_t)ul);
+				cur += 4 + ul;
+			}
+		} else {
+			/* readACL (zk-buffer.js:372-382): count x { perms, scheme, id } */
+			for (int32_t k = 0; k < count; ++k) {
+				if (cur + 4 > end) { ok = false; break; }
+				const int32_t perms = (int32_t)sm_be32(c.tile, cur);
+				cur += 4;
+				if (cur + 4 > end) { ok = false; break; }
+				const int32_t l0 = (int32_t)sm_be32(c.tile, cur);
+				const uint32_t u0 = l0 > 0 ? (uint32_t)l0 : 0u;
+				if (cur + 4 + u0 > end) { ok = false; break; }
+				const uint32_t p0 = cur + 4;
+				cur += 4 + u0;
+				if (cur + 4 > end) { ok = false; break; }
+				const int32_t l1 = (int32_t)sm_be32(c.tile, cur);
+				const uint32_t u1 = l1 > 0 ? (uint32_t)l1 : 0u;
+				if (cur + 4 + u1 > end) { ok = false; break; }
+				if (arow < o.cap_acl) { o.acl_frame[arow] = frame; o.acl_perms[arow] = perms; }
+				arow++;
+				put_buf(o, brow++, frame, cs + p0, (int32_t)u0);
+				put_buf(o, brow++, frame, cs + cur + 4, (int32_t)u1);
+				cur += 4 + u1;
+			}
+		}
+		if (ok) {
+			if (kind == VK_ACL_FLAGS) {                      /* CREATE request: flags follow the ACL */
+				if (cur + 4 > end) ok = false;
+				else a.o.a0[frame] = (int32_t)sm_be32(c.tile, cur);
+			} else if (kind != VK_STR) {                     /* a Stat follows the vector */
+				if (cur + 68 > end) ok = false;
+				else put_stat(o, c.tile, cur, srow, frame);
+			}
+		}
+		good = good && ok;
+	}
+	return good;
+}
+
+/* what one lane knows about its frame between the header stage and the row stage of a round */
+struct Fr {
+	uint32_t nst, nbf, nac;      /* rows the frame owns */
+	uint32_t b0, b1;             /* tile offsets of the length prefixes of up to two scalar buffers (0 = none) */
+	uint32_t st;                 /* tile offset of the Stat (0 = none) */
+	uint32_t vrel, vkind;        /* vector to be walked later */
+	uint32_t slow;               /* 1 = generic parser, 2 = generic parser and the frame reaches past the tile */
+};
+
+/* readRequest (zk-buffer.js:58-95,138-253) for a frame inside the tile: header, scalar fields and
+ * the row counts; false = leave it to the generic parser.  `pr` = tile offset of payload byte 0. */
+__device__ __forceinline__ bool direct_request(const uint8_t *t, const uint32_t pr, const uint32_t size, FrameCols &o, Fr &fr)
+{
+	if (size < 8) return false;
+	const int32_t xid = (int32_t)sm_be32(t, pr);
+	const int32_t op = (int32_t)sm_be32(t, pr + 4);
+	o.xid = xid; o.zxid = 0; o.err = 0; o.a0 = 0; o.a1 = 0;
+	/* opcodes whose body starts with a path: CREATE DELETE EXISTS GET_DATA SET_DATA GET_ACL GET_CHILDREN SYNC GET_CHILDREN2 */
+	const bool has_path = op >= 0 && op <= 12 && ((0x137Eu >> op) & 1u);
+	if (!has_path) {
+		if (op == ZKB_OP_SET_WATCHES) return false;      /* three vectors: counted by the generic parser */
+		/* 'Unsupported opcode' (zk-buffer.js:91-92), PING and CLOSE_SESSION included */
+		const int known = op_known(op) ? op : ZKB_OP_NONE;
+		o.meta = ZKB_ST_BAD_DECODE | ((uint32_t)(uint8_t)(int8_t)known << 8) | ((uint32_t)ZKB_KIND_REQUEST << 16) |
+		    (DETAIL(ZKB_CAUSE_UNSUPPORTED, ZKB_F_OPCODE) << 24);
+		return true;
+	}
+	/* path */
+	if (12 > size) return false;
+	const int32_t pl = (int32_t)sm_be32(t, pr + 8);
+	uint32_t cur = 12u + (pl > 0 ? (uint32_t)pl : 0u);
+	if (cur > size) return false;
+	fr.b0 = pr + 8; fr.nbf = 1;
+	/* data (CREATE, SET_DATA) */
+	if (op == ZKB_OP_CREATE || op == ZKB_OP_SET_DATA) {
+		if (cur + 4 > size) return false;
+		const int32_t dl = (int32_t)sm_be32(t, pr + cur);
+		fr.b1 = pr + cur;
+		cur += 4u + (dl > 0 ? (uint32_t)dl : 0u);
+		if (cur > size) return false;
+		fr.nbf = 2;
+	}
+	/* tail */
+	if (op == ZKB_OP_CREATE) {
+		if (cur + 4 > size) return false;
+		const int32_t n = (int32_t)sm_be32(t, pr + cur);
+		const uint32_t k = n > 0 ? (uint32_t)n : 0u;
+		fr.vrel = pr + cur; fr.vkind = VK_ACL_FLAGS;
+		fr.nbf += 2 * k; fr.nac = k;
+		o.a1 = (int32_t)k;                              /* a0 (flags) is written when the ACL has been walked */
+	} else if (op == ZKB_OP_DELETE || op == ZKB_OP_SET_DATA) {
+		if (cur + 4 > size) return false;
+		o.a0 = (int32_t)sm_be32(t, pr + cur);
+	} else if (op != ZKB_OP_GET_ACL && op != ZKB_OP_SYNC) {   /* watch flag (readBool asserts 0/1) */
+		if (!(cur < size)) return false;
+		const uint32_t b = t[pr + cur];
+		if (b > 1) return false;
+		o.a0 = (int32_t)b;
+	}
+	o.meta = ZKB_ST_OK | ((uint32_t)(uint8_t)(int8_t)op << 8) | ((uint32_t)ZKB_KIND_REQUEST << 16);
+	return true;
+}
+
+/* readResponse (zk-buffer.js:281-331) for a frame inside the tile */
+__device__ __forceinline__ bool direct_response(const uint8_t *t, const DecArgs &a, const uint32_t pr, const uint32_t size,
+    const uint32_t s, FrameCols &o, Fr &fr)
+{
+	if (size < 16) return false;
+	const int32_t xid = (int32_t)sm_be32(t, pr);
+	const int32_t err = (int32_t)sm_be32(t, pr + 12);
+	int op = special_xid(xid);
+	if (op == ZKB_OP_NONE && a.xt_ops) {
+		const int64_t idx = (int64_t)xid - (int64_t)__ldg(a.xt_base + s);
+		if (idx >= 0 && idx < (int64_t)__ldg(a.xt_count + s))
+			op = __ldg(a.xt_ops + __ldg(a.xt_off + s) + (uint64_t)idx);
+	}
+	if (op == ZKB_OP_NONE) return false;                 /* 'reply packet must match a request' */
+	o.xid = xid; o.err = err; o.a0 = 0; o.a1 = 0;
+	o.zxid = (int64_t)(((uint64_t)sm_be32(t, pr + 4) << 32) | (uint64_t)sm_be32(t, pr + 8));
+	o.meta = ZKB_ST_OK | ((uint32_t)(uint8_t)(int8_t)op << 8) | ((uint32_t)ZKB_KIND_RESPONSE << 16);
+	if (err != 0) return true;                           /* only 'OK' replies have a body */
+	if (op == ZKB_OP_GET_CHILDREN || op == ZKB_OP_GET_CHILDREN2 || op == ZKB_OP_GET_ACL) {
+		if (20 > size) return false;
+		const int32_t n = (int32_t)sm_be32(t, pr + 16);
+		const uint32_t k = n > 0 ? (uint32_t)n : 0u;
+		o.a0 = (int32_t)k;
+		fr.vrel = pr + 16;
+		if (op == ZKB_OP_GET_ACL) { fr.vkind = VK_ACL_STAT; fr.nbf = 2 * k; fr.nac = k; fr.nst = 1; }
+		else if (op == ZKB_OP_GET_CHILDREN2) { fr.vkind = VK_STR_STAT; fr.nbf = k; fr.nst = 1; }
+		else { fr.vkind = VK_STR; fr.nbf = k; }
+		return true;
+	}
+	uint32_t cur = 16;
+	if (op == ZKB_OP_NOTIFICATION) {
+		if (24 > size) return false;
+		o.a0 = (int32_t)sm_be32(t, pr + 16);
+		o.a1 = (int32_t)sm_be32(t, pr + 20);
+		cur = 24;
+	}
+	if (op == ZKB_OP_NOTIFICATION || op == ZKB_OP_CREATE || op == ZKB_OP_GET_DATA) {
+		if (cur + 4 > size) return false;
+		const int32_t l = (int32_t)sm_be32(t, pr + cur);
+		fr.b0 = pr + cur; fr.nbf = 1;
+		cur += 4u + (l > 0 ? (uint32_t)l : 0u);
+		if (cur > size) return false;
+	}
+	if (op == ZKB_OP_GET_DATA || op == ZKB_OP_EXISTS || op == ZKB_OP_SET_DATA) {
+		if (cur + 68 > size) return false;
+		fr.st = pr + cur; fr.nst = 1;
+		return true;
+	}
+	if (op == ZKB_OP_NOTIFICATION || op == ZKB_OP_CREATE) return true;
+	/* header only; everything else is 'Unsupported opcode' (zk-buffer.js:326-327): generic parser */
+	return op == ZKB_OP_SET_WATCHES || op == ZKB_OP_PING || op == ZKB_OP_SYNC || op == ZKB_OP_DELETE ||
+	    op == ZKB_OP_CLOSE_SESSION;
+}
+
+/* Everything one warp does for one 8 KiB chunk.  REDO == false: first rows from the splitter's
+ * prediction (a.g_rbase), verified; REDO == true: first rows from the scan over the chunks' real
+ * counts (a.c_base), chunks that need the exact body are skipped (they have their own launch). */
+template <int DIR, bool REDO>
+__device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c, uint64_t *bar, const uint32_t chunk,
+    const uint32_t lane)
+{
+	if (REDO && a.c_rows[chunk].x) return;
+	const uint64_t cs = (uint64_t)chunk << ZK_CHUNK_LOG2;
+	const uint64_t avail = a.nbytes_pad - cs;
+	const uint32_t wlen = avail < (uint64_t)ZK_WIN ? (uint32_t)avail : ZK_WIN;
+
+	/* ---- stage the chunk: one TMA bulk copy, completion on an mbarrier; the splitter's records of
+	 * the chunk are fetched while it is in flight ---- */
+	if (lane == 0) {
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+		mbar_expect_tx(bar, wlen);
+		bulk_g2s(c.tile, a.bytes + cs, wlen, bar);
+		*reinterpret_cast<uint4 *>(c.tile + wlen) = make_uint4(0, 0, 0, 0);
+	}
+	Rd rd;
+	rd.sm = c.tile; rd.lo = cs; rd.wlen = wlen; rd.g = a.bytes;
+
+	const uint32_t gsh = ZK_CHUNK_LOG2 - a.glog2;
+	const uint32_t g0 = chunk << gsh, g1 = (chunk + 1) << gsh;
+	const uint32_t f0 = a.g_base[g0];
+	const uint32_t f1 = (g1 < a.n_gran) ? a.g_base[g1] : (uint32_t)a.n_frames;
+	const uint32_t nfr = f1 - f0;
+	const bool last = (chunk == a.n_chunks - 1);
+	const uint64_t ce = last ? a.nbytes : cs + ZK_CHUNK;
+	const uint32_t sf = a.g_sf[g0];                  /* first session starting at or after cs */
+	uint64_t boff = ZK_NONE;                         /* boff[l] = sess_off[sf + l] */
+	if (sf + lane <= a.nsess) boff = __ldg(a.sess_off + sf + lane);
+	const uint64_t boff0 = __shfl_sync(0xffffffffu, boff, 0);
+	const bool cont = (boff0 != cs);                 /* the chunk starts inside session sf-1 */
+	uint32_t sfirst = 0;                             /* first frame (batch row) of that session */
+	if (cont) {
+		const uint32_t src = a.g_ssrc[g0];
+		if (src) sfirst = a.g_base[src - 1] + a.g_openlocal[(size_t)a.g_sel[src - 1] * a.n_gran + (src - 1)];
+	}
+	/* first rows of the chunk */
+	uint32_t e0, e1, e2, p0 = 0, p1 = 0, p2 = 0;
+	if (REDO) {
+		const uint4 cb = a.c_base[chunk];
+		e0 = cb.y; e1 = cb.z; e2 = cb.w;
+	} else {
+		const uint4 rb0 = a.g_rbase[g0], rb1 = a.g_rbase[g1 < a.n_gran ? g1 : a.n_gran];
+		e0 = rb0.x; e1 = rb0.y; e2 = rb0.z;
+		p0 = rb1.x - rb0.x; p1 = rb1.y - rb0.y; p2 = rb1.z - rb0.z;
+	}
+	/* where the chain stands inside this lane's 256-byte sub-range, from the splitter */
+	const uint64_t lo = cs + 256u * lane;
+	const uint64_t hi = (lo + 256 < ce) ? lo + 256 : ce;
+	uint64_t entry = ZK_NONE;
+	if (lo < ce) {
+		const uint32_t g = (uint32_t)(lo >> a.glog2);
+		const uint64_t gstart = (uint64_t)g << a.glog2;
+		const uint32_t subs = 1u << (a.glog2 - 8);
+		const uint16_t v = a.g_sub[((size_t)a.g_sel[g] * a.n_gran + g) * subs + (uint32_t)((lo - gstart) >> 8)];
+		if (v != 0xFFFFu) entry = gstart + v;
+	}
+	/* session the entry lies in: jl = boundaries sess_off[sf + l], l < 32, strictly below it */
+	uint32_t es = 0; uint64_t esend = 0; bool e_start = false;
+	{
+		const uint64_t e = (entry != ZK_NONE) ? entry : 0;
+		uint32_t jl = 0;
+#pragma unroll
+		for (int step = 16; step > 0; step >>= 1) {
+			const uint64_t bv = __shfl_sync(0xffffffffu, boff, (int)(jl + step - 1));
+			if (bv < e) jl += step;
+		}
+		{
+			const uint64_t bv = __shfl_sync(0xffffffffu, boff, 31);
+			if (jl == 31 && bv < e) jl = 32;
+		}
+		uint64_t b_at = __shfl_sync(0xffffffffu, boff, (int)(jl < 32 ? jl : 31));
+		uint64_t b_next = __shfl_sync(0xffffffffu, boff, (int)(jl + 1 < 32 ? jl + 1 : 31));
+		if (entry != ZK_NONE) {
+			uint32_t sprev = sf - 1 + jl;              /* last session that starts strictly before the entry */
+			if (jl >= 32) {                            /* > 32 session starts in this chunk: use the table */
+				uint32_t l2 = sf + 31, h2 = a.nsess;
+				while (h2 - l2 > 1) {
+					const uint32_t mid = (l2 + h2) >> 1;
+					if (__ldg(a.sess_off + mid) < entry) l2 = mid; else h2 = mid;
+				}
+				sprev = l2;
+				b_at = __ldg(a.sess_off + sprev + 1);
+			}
+			if (jl + 1 >= 32 || jl >= 32) b_next = (sprev + 2 <= a.nsess) ? __ldg(a.sess_off + sprev + 2) : ZK_NONE;
+			if (entry < b_at) { es = sprev; esend = b_at; }
+			else { es = sprev + 1; esend = b_next; e_start = true; }
+		}
+	}
+	__syncwarp();
+	mbar_wait(bar, 0);
+
+	/* ---- frame starts: count per lane, prefix over lanes ---- */
+	const uint32_t mycnt = walk_subrange<false>(a, c, cs, hi, entry, es, esend, 0, 0, false, 0, false);
+	const uint32_t lbase = warp_incl_scan(mycnt, lane) - mycnt;
+	if (lane == 31 && lbase + mycnt != nfr) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
+	if (last && lane == 0) {
+		/* empty sessions at the very end of the batch start at nbytes, in no sub-range */
+		for (uint32_t sx = a.nsess; sx > 0 && __ldg(a.sess_off + sx - 1) == a.nbytes; --sx) {
+			a.o.sess_consumed[sx - 1] = a.nbytes;
+			a.o.sess_bad_length_at[sx - 1] = ZK_NONE;
+			a.o.sess_first_frame[sx - 1] = (uint32_t)a.n_frames;
+		}
+	}
+	const bool one_session = cont && !(boff0 < ce || (last && sf < a.nsess));   /* no session starts inside */
+
+	uint32_t rs = 0, rb = 0, ra = 0;       /* rows of the chunk placed so far (stat, buf, acl) */
+	uint32_t nv = 0;                       /* vectors set aside */
+	bool good = true;
+	uint32_t n_slow = 0;
+	Parsed lp;                             /* the chunk's long frame (reaches past the tile), if this lane has it */
+	uint64_t l_foff = 0; int32_t l_flen = 0; uint32_t l_f = 0;
+	lp.n_stat = lp.n_buf = lp.n_acl = 0;
+
+	uint32_t wlo = 0;
+	do {
+		/* ---- tile offsets of frames wlo .. wlo + ZK_FREL_CAP - 1; the first window also does the
+		 * per-session bookkeeping ---- */
+		walk_subrange<true>(a, c, cs, hi, entry, es, esend, wlo, lbase, wlo == 0, f0 + lbase, e_start);
+		__syncwarp();
+		const uint32_t wend = (nfr - wlo < ZK_FREL_CAP) ? nfr : wlo + ZK_FREL_CAP;
+		for (uint32_t k0 = wlo; k0 < wend; k0 += 32) {
+			if (nv > ZK_VL_CAP - 32) {
+				__syncwarp();
+				good = drain_vectors(a, c, cs, f0, e0, e1, e2, nv, lane) && good;
+				nv = 0;
+				__syncwarp();
+			}
+			const uint32_t k = k0 + lane;
+			const bool valid = k < wend;
+			const uint32_t rel = valid ? c.frel[k - wlo] : 0u;
+			const uint32_t f = f0 + k;
+			const uint64_t foff = cs + rel;
+			const int32_t flen = valid ? (int32_t)sm_be32(c.tile, rel) : 0;
+			/* which session, and where that session's frames begin */
+			uint32_t s = sf - 1, first = sfirst;
+			if (!one_session) {
+				uint32_t j = 0;            /* boundaries sess_off[sf + l], l < 32, at or below the frame */
+#pragma unroll
+				for (int step = 16; step > 0; step >>= 1) {
+					const uint64_t bv = __shfl_sync(0xffffffffu, boff, (int)(j + step - 1));
+					if (bv <= foff) j += step;
+				}
+				{
+					const uint64_t bv = __shfl_sync(0xffffffffu, boff, 31);
+					if (j == 31 && bv <= foff) j = 32;
+				}
+				if (j == 32 && valid) {
+					uint32_t l2 = sf + 31, h2 = a.nsess;          /* last s with sess_off[s] <= foff */
+					while (h2 - l2 > 1) {
+						const uint32_t mid = (l2 + h2) >> 1;
+						if (__ldg(a.sess_off + mid) <= foff) l2 = mid; else h2 = mid;
+					}
+					s = l2;
+				} else if (j) {
+					s = sf + j - 1;
+				}
+				/* a session that starts inside the chunk had its first frame written by the walk above
+				 * (same warp, ordered by the __syncwarp) */
+				if (valid && s != sf - 1) first = __ldcg(a.o.sess_first_frame + s);
+			}
+			Fr fr;
+			fr.nst = fr.nbf = fr.nac = 0; fr.b0 = fr.b1 = fr.st = 0; fr.vrel = 0; fr.vkind = 0; fr.slow = 0;
+			if (valid) {
+				a.o.frame_off[f] = foff;
+				a.o.frame_len[f] = flen;
+				a.o.session[f] = s;
+				const bool inwin = rel + 4u + (uint32_t)flen <= wlen;
+				const bool server = DIR == 1 ? true : DIR == 2 ? false : (a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER));
+				const uint32_t hs = a.sess_hs ? __ldg(a.sess_hs + s) : 1u;
+				const uint32_t idx = f - first;
+				FrameCols o;
+				bool done = false;
+				if (inwin && idx >= hs)
+					done = server ? direct_request(c.tile, rel + 4, (uint32_t)flen, o, fr)
+					              : direct_response(c.tile, a, rel + 4, (uint32_t)flen, s, o, fr);
+				if (!done) {
+					/* handshake frames, malformed frames, frames longer than the tile: exact reader */
+					Parsed p;
+					n_slow++;
+					parse_frame<DIR>(rd, a, foff, flen, s, idx, p);
+					o.meta = p.meta; o.xid = p.xid; o.zxid = p.zxid; o.err = p.err; o.a0 = p.a0; o.a1 = p.a1;
+					fr.nst = fr.nbf = fr.nac = 0; fr.b0 = fr.b1 = fr.st = 0; fr.vrel = 0; fr.vkind = 0;
+					if (p.n_stat | p.n_buf | p.n_acl) {
+						if (inwin) { fr.slow = 1; fr.nst = p.n_stat; fr.nbf = p.n_buf; fr.nac = p.n_acl; }
+						else { fr.slow = 2; lp = p; l_foff = foff; l_flen = flen; l_f = f; }
+					}
+				}
+				a.o.meta[f] = o.meta;
+				a.o.xid[f] = o.xid;
+				a.o.zxid[f] = o.zxid;
+				a.o.err[f] = o.err;
+				a.o.a0[f] = o.a0;
+				a.o.a1[f] = o.a1;
+			}
+			/* ---- every frame's first rows: one scan over the round (buf and acl counts share a word;
+			 * at most one Stat per frame) ---- */
+			const uint32_t packed = fr.nbf | (fr.nac << 17);
+			const uint32_t inc = warp_incl_scan(packed, lane);
+			const uint32_t stm = __ballot_sync(0xffffffffu, fr.nst != 0);
+			const uint32_t ex = inc - packed;
+			const uint32_t brow = e1 + rb + (ex & 0x1ffffu), arow = e2 + ra + (ex >> 17);
+			const uint32_t srow = e0 + rs + __popc(stm & ((1u << lane) - 1u));
+			const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31);
+			/* ---- rows ---- */
+			if (fr.slow == 1) {
+				Parsed p;
+				const bool server = DIR == 1 ? true : DIR == 2 ? false : (a.sess_flags && (__ldg(a.sess_flags + s) & ZKB_SESS_SERVER));
+				(void)server;
+				parse_frame<DIR>(rd, a, foff, flen, s, f - first, p);
+				emit_side(rd, a, foff, flen, p, f, srow, brow, arow);
+			} else {
+				if (fr.b0) put_buf(a.o, brow, f, cs + fr.b0 + 4, max((int32_t)sm_be32(c.tile, fr.b0), 0));
+				if (fr.b1) put_buf(a.o, brow + 1, f, cs + fr.b1 + 4, max((int32_t)sm_be32(c.tile, fr.b1), 0));
+				if (fr.st) put_stat(a.o, c.tile, fr.st, srow, f);
+			}
+			/* vectors wait for the drain */
+			const uint32_t vm = __ballot_sync(0xffffffffu, fr.vkind != 0);
+			if (fr.vkind) {
+				VEnt e;
+				e.w0 = (rel + 4) | (fr.vrel << 16);
+				e.w1 = (brow + (fr.b0 ? 1u : 0u) + (fr.b1 ? 1u : 0u) - e1) | ((arow - e2) << 16);
+				e.w2 = (srow - e0) | (fr.vkind << 16);
+				e.w3 = k;
+				c.vl[nv + __popc(vm & ((1u << lane) - 1u))] = e;
+			}
+			nv += __popc(vm);
+			rb += tot & 0x1ffffu; ra += tot >> 17; rs += __popc(stm);
+		}
+		wlo += ZK_FREL_CAP;
+		__syncwarp();
+	} while (wlo < nfr);
+	__syncwarp();
+	if (nv) good = drain_vectors(a, c, cs, f0, e0, e1, e2, nv, lane) && good;
+	good = __all_sync(0xffffffffu, good);
+	n_slow = warp_sum(n_slow);
+	if (lane == 0 && n_slow) atomicAdd(&a.ctrl->n_slow, (unsigned long long)n_slow);
+
+	/* the long frame's rows come last: it is the chunk's last frame */
+	const uint32_t ts = rs + warp_sum(lp.n_stat), tb = rb + warp_sum(lp.n_buf), ta = ra + warp_sum(lp.n_acl);
+	if (lp.n_stat | lp.n_buf | lp.n_acl)
+		emit_side(rd, a, l_foff, l_flen, lp, l_f, e0 + rs, e1 + rb, e2 + ra);
+	if (!REDO && lane == 0) {
+		/* what the chunk really has (a frame that broke its promise owns no rows: the exact body
+		 * counts them when the chunk is done again) */
+		a.c_rows[chunk] = make_uint4(good ? 0u : 1u, ts, tb, ta);
+		if (!good || ts != p0 || tb != p1 || ta != p2) {
+			atomicOr(&a.ctrl->error, ZK_DERR_MISPREDICT);
+			atomicMin(&a.ctrl->first_bad, chunk);
+		}
+	}
+}

@@ -43,6 +43,7 @@ struct zk_ctrl {
 	unsigned long long prof[8];  /* ZK_PROFILE_PHASES builds: cycles per decode phase, chunk count */
 	unsigned int       pred_rows[3]; /* the splitter's predicted STAT / BUF / ACL row totals of the batch */
 	unsigned int       dir_mask;     /* 1 = some session is client->server, 2 = some is server->client (k_check_sessions) */
+	unsigned int       first_dirty[2]; /* n_dirty / n_rewalk after the first scan of a split (k_split_round) */
 };
 
 struct zkb_ctx {

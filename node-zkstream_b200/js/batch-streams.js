@@ -8,7 +8,13 @@
  * `require` this file from lib/connection-fsm.js:86-91 instead of './zk-streams' to switch
  * a client over; pass {batchBytes: n} to collect n bytes before each GPU call when
  * replaying captures (0, the default, decodes every chunk as it arrives, like the
- * reference).
+ * reference).  The reference asks fsm.isInState('handshaking') once per FRAME
+ * (lib/zk-streams.js:68); one GPU call covers many frames, so a batching replay says how many
+ * leading frames of the stream are handshake frames with {handshakeFrames: n} (1 for a
+ * connection captured from its start) instead of being asked per call.  With batchBytes > 0 the
+ * xid map is read when the batch is decoded, not per frame: a capture that re-uses an xid inside
+ * one batch resolves it to the later opcode (cut such captures into quiescent segments, see
+ * include/zkcapture.h).
  *
  * Needs a node with N-API (>= 8.x) and the built addon; neither exists in the build image,
  * so both streams are exercised in the reference's own JavaScript engine against a recorded
@@ -36,19 +42,36 @@ function context() {
 	return (ctx);
 }
 
-/* fsm.zcf_xidMap ({xid: opcode name}) -> dense Int8Array starting at xid 0 */
-function xidTable(map) {
-	var max = -1;
-	Object.keys(map).forEach(function (k) { k = parseInt(k, 10); if (k > max) max = k; });
-	var ops = new Int8Array(max + 1);
-	for (var i = 0; i <= max; ++i) ops[i] = -128;
-	Object.keys(map).forEach(function (k) {
-		var code = mod_consts.OP_CODES[map[k]];
-		k = parseInt(k, 10);
-		if (k >= 0 && code !== undefined) ops[k] = code;
-	});
-	return (ops);
+/* fsm.zcf_xidMap ({xid: opcode name}) -> dense Int8Array starting at xid 0.  The map only ever
+ * grows (the reference never deletes from it), so the table is kept between calls and only keys
+ * that are new, or whose opcode changed, are written; it is rebuilt when the map object changes. */
+function XidTable() {
+	this.map = null;
+	this.seen = {};
+	this.nseen = 0;
+	this.ops = new Int8Array(0);
 }
+XidTable.prototype.update = function (map) {
+	var self = this;
+	if (map !== this.map) { this.map = map; this.seen = {}; this.nseen = 0; this.ops = new Int8Array(0); }
+	var keys = Object.keys(map);
+	var max = this.ops.length - 1;
+	keys.forEach(function (k) { k = parseInt(k, 10); if (k > max) max = k; });
+	if (max + 1 > this.ops.length) {
+		var cap = Math.max(max + 1, this.ops.length * 2);
+		var grown = new Int8Array(cap);
+		for (var i = 0; i < cap; ++i) grown[i] = (i < this.ops.length) ? this.ops[i] : -128;
+		this.ops = grown;
+	}
+	keys.forEach(function (k) {
+		if (self.seen[k] === map[k]) return;
+		self.seen[k] = map[k];
+		var code = mod_consts.OP_CODES[map[k]];
+		var x = parseInt(k, 10);
+		if (x >= 0) self.ops[x] = (code !== undefined) ? code : -128;
+	});
+	return (this.ops);
+};
 
 function ZKDecodeStream(opts) {
 	mod_assert.object(opts, 'options');
@@ -59,6 +82,9 @@ function ZKDecodeStream(opts) {
 	this.zd_pending = [];
 	this.zd_used = 0;
 	this.zd_batch = opts.batchBytes || 0;
+	mod_assert.optionalNumber(opts.handshakeFrames, 'options.handshakeFrames');
+	this.zd_hsFrames = (opts.handshakeFrames === undefined) ? null : opts.handshakeFrames;
+	this.zd_xids = new XidTable();
 	opts.readableObjectMode = true;
 	opts.writableObjectMode = false;
 	mod_stream.Transform.call(this, opts);
@@ -87,9 +113,14 @@ ZKDecodeStream.prototype._flush = function (cb) {
 ZKDecodeStream.prototype.decodePending = function () {
 	var self = this;
 	var data = Buffer.concat(this.zd_pending, this.zd_used);
-	var hs = this.zd_fsm.isInState('handshaking') ? 0xffffffff : 0;
+	/* handshake depth: as many leading frames as the caller said are still owed, else what the fsm
+	 * says now for the whole call (exact when every call holds one frame, as on a live socket) */
+	var hs = (this.zd_hsFrames !== null) ? this.zd_hsFrames :
+	    (this.zd_fsm.isInState('handshaking') ? 0xffffffff : 0);
 	var cols = addon.decodeHost(context(), data, this.zd_server ? 1 : 0, hs,
-	    this.zd_server ? null : xidTable(this.zd_fsm.zcf_xidMap));
+	    this.zd_server ? null : this.zd_xids.update(this.zd_fsm.zcf_xidMap));
+	if (this.zd_hsFrames !== null)
+		this.zd_hsFrames = Math.max(0, this.zd_hsFrames - cols.n_frames);
 	var ok = true;
 	new Materialiser(cols, data).forEach(0, function (pkt) {
 		self.push(pkt);

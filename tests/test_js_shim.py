@@ -173,9 +173,12 @@ def test_js_batch_decode_stream_with_recorded_addon(oracle, synth, zk):
             hsv = np.array([0xFFFFFFFF if i == 0 else 0], dtype=np.uint32)
             cols = oracle.decode(np.frombuffer(pend, dtype=np.uint8), None, flags, hsv, xt)
             consumed = int(cols.sess_consumed[0])
-            table[pend.hex() + ("S" if s["isServer"] else "C") + ("H" if i == 0 else "N")] = _cols_js(cols, zk, consumed)
+            table[pend.hex() + ("S" if s["isServer"] else "C") + "h%d" % int(hsv[0])] = _cols_js(cols, zk, consumed)
             stuck = int(cols.sess_bad_length_at[0]) != zk._abi.NO_OFFSET
             carry = pend[consumed:]
+        # the batching replay: the whole stream in one GPU call, told that its first frame is the handshake
+        whole = oracle.decode(np.frombuffer(data, dtype=np.uint8), None, flags, np.array([1], dtype=np.uint32), xt)
+        table[data.hex() + ("S" if s["isServer"] else "C") + "h1"] = _cols_js(whole, zk, int(whole.sess_consumed[0]))
         names = {str(k): zk.consts.OP_CODE_LOOKUP[v] for k, v in xm.items()}
         sess_js.append("{isServer:%s,xidMap:%s,chunks:[%s]}" % (
             "true" if s["isServer"] else "false", json.dumps(names), ",".join(json.dumps(c.hex()) for c in chunks)))
@@ -188,7 +191,7 @@ def test_js_batch_decode_stream_with_recorded_addon(oracle, synth, zk):
         src["materialise.js"], src["flatten.js"],
         "var CUR = { server: false, hs: true };",
         "var fakeAddon = { createContext: function () { return {}; }, decodeHost: function (ctx, data, isServer, hs, ops) {",
-        "  var key = data.toString('hex') + (isServer ? 'S' : 'C') + (hs ? 'H' : 'N');",
+        "  var key = data.toString('hex') + (isServer ? 'S' : 'C') + 'h' + hs;",
         "  if (!TABLE[key]) throw new Error('unrecorded decodeHost call ' + key.slice(-40));",
         "  CUR.ops = ops; return TABLE[key]; } };",
         "DEFS['batch-streams'] = function (module, exports, require) {\n" + src["batch-streams.js"] + "\n};",
@@ -227,16 +230,37 @@ for (var si = 0; si < SESS.length; ++si) {
 		else if (ev.ev === 'error') out.push('{"error":{"code":' + jstr(ev.arg.code) + ',"message":' + jstr(ev.arg.message) + '}}');
 	}
 	print('{"opsOk":' + (opsOk ? 'true' : 'false') + ',"events":[' + out.join(',') + ']}');
+	/* the same stream as a batching replay: nothing is decoded until the flush, the fsm is not in its
+	 * handshaking state any more, and handshakeFrames says that the first frame is the connect frame */
+	var fsm2 = { zcf_xidMap: sess.xidMap, isInState: function (st) { return (false); } };
+	var bs = new BatchDecode({ fsm: fsm2, isServer: sess.isServer, batchBytes: 1073741824, handshakeFrames: 1 });
+	var cbs = 0;
+	for (var i2 = 0; i2 < sess.chunks.length; ++i2)
+		bs._transform(hex(sess.chunks[i2]), null, function () { cbs++; });
+	var early = bs._events.length;
+	bs._flush(function () { });
+	var out2 = [];
+	for (var e2 = 0; e2 < bs._events.length; ++e2) {
+		var ev2 = bs._events[e2];
+		if (ev2.push !== undefined) out2.push('{"pkt":' + canon(ev2.push) + '}');
+		else if (ev2.ev === 'error') out2.push('{"error":{"code":' + jstr(ev2.arg.code) + ',"message":' + jstr(ev2.arg.message) + '}}');
+	}
+	print('{"batched":true,"early":' + early + ',"cbs":' + cbs + ',"chunks":' + sess.chunks.length + ',"events":[' + out2.join(',') + ']}');
 }
 """])
     driver = "var SESS = [" + ",".join(sess_js) + "];\n" + driver
     out = ref_js.run_js(driver)
     lines = [l for l in out.splitlines() if l.strip()]
-    assert len(lines) == len(chosen)
-    for line, (s, _, _) in zip(lines, chosen):
+    assert len(lines) == 2 * len(chosen)
+    for line, line2, (s, _, _) in zip(lines[0::2], lines[1::2], chosen):
         got = ref_js._decanon(json.loads(line))
         assert got["opsOk"] is True
         assert canon_events(got["events"]) == s["events"], s["corpus"]
+        # batchBytes > 0 with handshakeFrames: 1 — every write acknowledged, nothing pushed before the
+        # flush, and then exactly what the reference's stream produced, connect frame included
+        got2 = ref_js._decanon(json.loads(line2))
+        assert got2["batched"] is True and got2["early"] == 0 and got2["cbs"] == got2["chunks"]
+        assert canon_events(got2["events"]) == s["events"], s["corpus"]
 
 
 def test_js_batch_encode_stream_with_recorded_addon(oracle, zk):
