@@ -147,8 +147,20 @@ __device__ __forceinline__ uint32_t lower_bound_u64(const uint64_t *off, uint32_
 /* Does a frame header that makes sense for this direction start at p?  Ranking only:
  * a wrong answer costs a FIX iteration, never a wrong result.  Both words are loaded
  * before either is tested so the two misses overlap. */
+/* replies: is this xid one the session's table covers, or a special one (zk-buffer.js:275-279)?  A reply
+ * with any other xid cannot be decoded ('reply packet must match a request'), so a candidate that has
+ * one is far more likely payload that happens to look like a header */
+struct XidWin { int64_t base, count; bool on; };
+__device__ __forceinline__ bool xid_plausible(const XidWin &w, int32_t xid)
+{
+	if (!w.on) return true;
+	if (xid == ZKB_XID_NOTIFICATION || xid == ZKB_XID_PING || xid == ZKB_XID_AUTH || xid == ZKB_XID_SET_WATCHES) return true;
+	const int64_t idx = (int64_t)xid - w.base;
+	return idx >= 0 && idx < w.count;
+}
+
 __device__ bool header_plausible(const uint8_t *bytes, uint64_t p, uint64_t send, bool server,
-    uint64_t &next)
+    uint64_t &next, const XidWin &xw)
 {
 	const uint32_t fld = server ? 8u : 16u;      /* type (requests) / err (responses) */
 	if (p + 4 + fld + 4 > send) return false;
@@ -157,18 +169,19 @@ __device__ bool header_plausible(const uint8_t *bytes, uint64_t p, uint64_t send
 	if (len < (int32_t)fld || len > ZKB_MAX_PACKET) return false;
 	if (p + 4 + (uint64_t)len > send) return false;
 	if (server ? !op_known(f) : !err_known(f)) return false;
+	if (!server && xw.on && !xid_plausible(xw, (int32_t)g_be32(bytes, p + 4))) return false;
 	next = p + 4 + (uint64_t)len;
 	return true;
 }
 
 /* Follow the chain `hops` more frames from q: a false start almost never survives this,
  * a true one always does (a legitimately incomplete or final frame ends the check). */
-__device__ bool chain_plausible(const uint8_t *bytes, uint64_t q, uint64_t send, bool server, int hops)
+__device__ bool chain_plausible(const uint8_t *bytes, uint64_t q, uint64_t send, bool server, int hops, const XidWin &xw)
 {
 	for (int k = 0; k < hops; ++k) {
 		if (q == send || q + 4 > send) return true;
 		uint64_t n2;
-		if (!header_plausible(bytes, q, send, server, n2)) {
+		if (!header_plausible(bytes, q, send, server, n2, xw)) {
 			/* the chain may end in a frame that is not complete yet, but only one whose
 			 * header is sane: a wild length that overruns the session proves nothing */
 			const uint32_t fld = server ? 8u : 16u;
@@ -183,24 +196,6 @@ __device__ bool chain_plausible(const uint8_t *bytes, uint64_t q, uint64_t send,
 	return true;
 }
 
-/* word J (0..11) of the 48-byte window held in three uint4 registers */
-template <int J>
-__device__ __forceinline__ uint32_t win_word(const uint4 &a, const uint4 &b, const uint4 &c)
-{
-	if constexpr (J == 0) return a.x; else if constexpr (J == 1) return a.y;
-	else if constexpr (J == 2) return a.z; else if constexpr (J == 3) return a.w;
-	else if constexpr (J == 4) return b.x; else if constexpr (J == 5) return b.y;
-	else if constexpr (J == 6) return b.z; else if constexpr (J == 7) return b.w;
-	else if constexpr (J == 8) return c.x; else if constexpr (J == 9) return c.y;
-	else if constexpr (J == 10) return c.z; else return c.w;
-}
-/* big-endian int32 at byte K (0..43) of the window */
-template <int K>
-__device__ __forceinline__ int32_t win_be32(const uint4 &a, const uint4 &b, const uint4 &c)
-{
-	return (int32_t)bswap32(__funnelshift_r(win_word<K / 4>(a, b, c), win_word<K / 4 + 1>(a, b, c), (K % 4) * 8));
-}
-
 #ifndef ZK_GUESS_HOPS
 #define ZK_GUESS_HOPS 3
 #endif
@@ -209,40 +204,64 @@ __device__ __forceinline__ int32_t win_be32(const uint4 &a, const uint4 &b, cons
 #endif
 struct GuessCtx {
 	const uint8_t *bytes;
-	uint64_t lim, send;
+	uint64_t lim, send, padend;
 	bool server;
+	XidWin xw;
 };
 
-/* local test of the candidate at byte K of the window that starts at absolute position blk:
- * sane length that fits the session, err code / opcode where the header would have it */
-template <int K>
-__device__ __forceinline__ uint32_t guess_at(const GuessCtx &g, uint64_t blk, uint32_t m, const uint4 &v0,
-    const uint4 &v1, const uint4 &v2)
+/* bit i = byte i of w is zero (exact: no false positives), i = 0 is the byte at the lowest address */
+__device__ __forceinline__ uint32_t nib_zero(uint32_t w)
 {
-	if (!((m >> K) & 1)) return 0;
-	const uint64_t p = blk + K;
-	if (p >= g.lim) return 0;
-	const int32_t len = win_be32<K>(v0, v1, v2);
-	if (len < (g.server ? 8 : 16) || len > ZKB_MAX_PACKET) return 0;
-	if (p + 4 + (uint64_t)len > g.send) return 0;
-	const int32_t f = g.server ? win_be32<K + 8>(v0, v1, v2) : win_be32<K + 16>(v0, v1, v2);
-	if (g.server ? !op_known(f) : !err_known(f)) return 0;
+	const uint32_t t = ~(((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w | 0x7f7f7f7fu);   /* 0x80 in every zero byte */
+	return (((t >> 7) * 0x00204081u) >> 21) & 0xfu;
+}
+__device__ __forceinline__ uint32_t mask16_zero(const uint4 &v)
+{
+	return nib_zero(v.x) | (nib_zero(v.y) << 4) | (nib_zero(v.z) << 8) | (nib_zero(v.w) << 12);
+}
+__device__ __forceinline__ uint32_t mask16_ff(const uint4 &v)
+{
+	return nib_zero(~v.x) | (nib_zero(~v.y) << 4) | (nib_zero(~v.z) << 8) | (nib_zero(~v.w) << 12);
+}
+__device__ __forceinline__ uint32_t mask16_le1(const uint4 &v)
+{
+	return nib_zero(v.x & 0xfefefefeu) | (nib_zero(v.y & 0xfefefefeu) << 4) | (nib_zero(v.z & 0xfefefefeu) << 8) |
+	    (nib_zero(v.w & 0xfefefefeu) << 12);
+}
+
+/* local test of the candidate at p: sane length that fits the session, err code / opcode (and, with a
+ * table, an xid the session can have) where the header would have them.  The bytes come through
+ * the L1: the scan has just loaded them. */
+__device__ bool guess_local(const GuessCtx &g, uint64_t p)
+{
+	if (p >= g.lim || p + 24 > g.padend) return false;
+	const int32_t len = (int32_t)g_be32(g.bytes, p);
+	if (len < (g.server ? 8 : 16) || len > ZKB_MAX_PACKET) return false;
+	if (p + 4 + (uint64_t)len > g.send) return false;
+	const int32_t f = (int32_t)g_be32(g.bytes, p + (g.server ? 8 : 16));
+	if (g.server ? !op_known(f) : !err_known(f)) return false;
+	if (!g.server && g.xw.on && !xid_plausible(g.xw, (int32_t)g_be32(g.bytes, p + 4))) return false;
 #ifndef ZK_GUESS_NO_PATHCHECK
 	/* a request that carries a path has its length next and '/' as its first byte; a real frame
 	 * that fails this (an empty path) only costs the granule a fix-up */
 	if (g.server && ((f >= 1 && f <= 6) || f == 8 || f == 9 || f == 12)) {
-		const int32_t pl = win_be32<K + 12>(v0, v1, v2);
-		if (pl < 1 || pl + 12 > len || ((uint32_t)win_be32<K + 16>(v0, v1, v2) >> 24) != 0x2fu) return 0;
+		const int32_t pl = (int32_t)g_be32(g.bytes, p + 12);
+		if (pl < 1 || pl + 12 > len || __ldg(g.bytes + p + 16) != 0x2fu) return false;
 	}
 #endif
-	return 1u << K;
+	return true;
 }
 
-/* First position in [gs, min(ge, send)) that looks like a frame start.  The granule is
- * scanned 16 bytes per load, 64 bytes per round: positions that pass the local test are
- * collected in a bit mask, then checked by following the chain three more frames.  Keeping
- * the far (DRAM-latency) checks out of the scan loop lets the lanes of a warp, which scan
- * different granules, issue them together instead of one lane at a time. */
+/* First position in [gs, min(ge, send)) that looks like a frame start.  The granule is scanned 16
+ * bytes per load.  Three byte-class masks over the 48 bytes in hand (byte <= 1: a length of at most
+ * 16 MiB starts with 0x00 or 0x01; byte == 0; byte == 0xff) say, with a few shifts and ANDs for all
+ * 16 positions of a load at once, where a header could start at all: a request has the three high
+ * bytes of a small opcode eight bytes in, a reply the four bytes of err 0 - or the three 0xff of a
+ * negative err - sixteen bytes in.  Only those few positions get the local test, and what passes it
+ * is checked by following the chain; the far (DRAM-latency) checks are made after each 128-byte
+ * segment so the lanes of a warp, which scan different granules, issue them together.  (Requests
+ * with a negative opcode are not proposed: a granule that starts with one takes the next frame and is
+ * put right by the fix-up.) */
 __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uint64_t ge, uint64_t send)
 {
 	GuessCtx g;
@@ -250,50 +269,45 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 	g.server = a.sess_flags && (a.sess_flags[s] & ZKB_SESS_SERVER);
 	g.lim = ge < send ? ge : send;
 	g.send = send;
+	g.xw.on = a.xt_ops != NULL && !g.server;
+	g.xw.base = g.xw.on ? (int64_t)__ldg(a.xt_base + s) : 0;
+	g.xw.count = g.xw.on ? (int64_t)__ldg(a.xt_count + s) : 0;
 	const uint64_t padend = (a.nbytes + 15) & ~15ull;
-	uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0, v2 = v0;
+	g.padend = padend;
+	const uint4 zero4 = make_uint4(0, 0, 0, 0);
+	uint4 v0 = zero4, v1 = zero4, v2 = zero4;
 	if (gs + 16 <= padend) v0 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs));
 	if (gs + 32 <= padend) v1 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs + 16));
+	uint32_t z0 = mask16_zero(v0), z1 = mask16_zero(v1);
+	uint32_t f0 = g.server ? 0u : mask16_ff(v0), f1 = g.server ? 0u : mask16_ff(v1);
 	for (uint64_t seg = gs; seg < g.lim; seg += 128) {
-		/* phase 1: local tests only, the lanes of a warp stay in step */
+		/* phase 1: masks only, the lanes of a warp stay in step */
 		uint64_t cand_lo = 0, cand_hi = 0;
 #pragma unroll 1
 		for (int q = 0; q < 8; ++q) {
 			const uint64_t blk = seg + 16 * q;
-			v2 = make_uint4(0, 0, 0, 0);
+			v2 = zero4;
 			if (blk + 48 <= padend) v2 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + blk + 32));
-			/* bytes <= 1 in the first 16 (a length <= 16 MiB starts with 0x00 or 0x01); the
-			 * zero-byte trick may flag extra bytes, every hit is re-checked in guess_at */
-			uint32_t m = 0;
-			{
-				const uint32_t ww[4] = { v0.x, v0.y, v0.z, v0.w };
-#pragma unroll
-				for (int j = 0; j < 4; ++j) {
-					uint32_t t = ww[j] & 0xFEFEFEFEu;
-					uint32_t z = (t - 0x01010101u) & ~t & 0x80808080u;
-					m |= (((z >> 7) & 1) | ((z >> 14) & 2) | ((z >> 21) & 4) | ((z >> 28) & 8)) << (4 * j);
+			const uint32_t z2 = mask16_zero(v2);
+			const uint32_t f2 = g.server ? 0u : mask16_ff(v2);
+			if (blk < g.lim) {
+				const uint64_t Z = (uint64_t)z0 | ((uint64_t)z1 << 16) | ((uint64_t)z2 << 32);
+				uint32_t c = mask16_le1(v0);
+				if (g.server) {
+					c &= (uint32_t)(Z >> 8) & (uint32_t)(Z >> 9) & (uint32_t)(Z >> 10);
+				} else {
+					const uint64_t F = (uint64_t)f0 | ((uint64_t)f1 << 16) | ((uint64_t)f2 << 32);
+					const uint32_t e0 = (uint32_t)(Z >> 16) & (uint32_t)(Z >> 17) & (uint32_t)(Z >> 18) & (uint32_t)(Z >> 19);
+					const uint32_t en = (uint32_t)(F >> 16) & (uint32_t)(F >> 17) & (uint32_t)(F >> 18);
+					c &= (e0 | en);
 				}
-			}
-			if (m && blk < g.lim) {
-				uint32_t c = guess_at<0>(g, blk, m, v0, v1, v2) | guess_at<1>(g, blk, m, v0, v1, v2) |
-				    guess_at<2>(g, blk, m, v0, v1, v2) | guess_at<3>(g, blk, m, v0, v1, v2) |
-				    guess_at<4>(g, blk, m, v0, v1, v2) | guess_at<5>(g, blk, m, v0, v1, v2) |
-				    guess_at<6>(g, blk, m, v0, v1, v2) | guess_at<7>(g, blk, m, v0, v1, v2) |
-				    guess_at<8>(g, blk, m, v0, v1, v2) | guess_at<9>(g, blk, m, v0, v1, v2) |
-				    guess_at<10>(g, blk, m, v0, v1, v2) | guess_at<11>(g, blk, m, v0, v1, v2) |
-				    guess_at<12>(g, blk, m, v0, v1, v2) | guess_at<13>(g, blk, m, v0, v1, v2) |
-				    guess_at<14>(g, blk, m, v0, v1, v2) | guess_at<15>(g, blk, m, v0, v1, v2);
+				c &= 0xffffu;
 				if (q < 4) cand_lo |= (uint64_t)c << (16 * q);
 				else cand_hi |= (uint64_t)c << (16 * (q - 4));
 			}
-			v0 = v1; v1 = v2;
+			v0 = v1; v1 = v2; z0 = z1; z1 = z2; f0 = f1; f1 = f2;
 		}
-#ifdef ZK_PROFILE_PHASES
-		const long long gp_t0 = clock64();
-		atomicAdd(&a.ctrl->prof[4], 1ull);                                   /* segments scanned (per lane) */
-		atomicAdd(&a.ctrl->prof[5], (unsigned long long)(__popcll(cand_lo) + __popcll(cand_hi)));  /* candidates */
-#endif
-		/* phase 2: the far checks, candidate by candidate in stream order */
+		/* phase 2: local test, then the far checks, candidate by candidate in stream order */
 #pragma unroll 1
 		for (int half = 0; half < 2; ++half) {
 			uint64_t cand = half ? cand_hi : cand_lo;
@@ -301,18 +315,12 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 				const int k = __ffsll((long long)cand) - 1;
 				cand &= cand - 1;
 				const uint64_t p = seg + 64 * half + (uint64_t)k;
+				if (!guess_local(g, p)) continue;
 				const int32_t len = (int32_t)g_be32(a.bytes, p);
-				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS)) {
-#ifdef ZK_PROFILE_PHASES
-					atomicAdd(&a.ctrl->prof[3], (unsigned long long)(clock64() - gp_t0));
-#endif
+				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS, g.xw))
 					return p;
-				}
 			}
 		}
-#ifdef ZK_PROFILE_PHASES
-		atomicAdd(&a.ctrl->prof[3], (unsigned long long)(clock64() - gp_t0));     /* cycles in phase 2 (per lane) */
-#endif
 	}
 	return ZK_NONE;
 }
@@ -1023,6 +1031,12 @@ struct __align__(16) ChunkSm {
 			uint16_t frel[ZK_FREL_CAP];    /* tile offset of frame (window start + i) */
 		};
 	};
+	/* direct body: the chunk's one frame that reaches past the tile, parsed by the lane that met it */
+	Parsed   lp;
+	uint64_t l_foff;
+	int32_t  l_flen;
+	uint32_t l_f;
+	uint32_t have_long;
 };
 
 enum { WALK_COUNT = 0, WALK_EMIT = 1, WALK_MARK = 2 };

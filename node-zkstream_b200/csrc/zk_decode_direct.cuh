@@ -74,6 +74,32 @@ __device__ __forceinline__ uint32_t walk_subrange(const DecArgs &a, ChunkSm &c, 
 	return cnt;
 }
 
+/* The same loop for the ordinary case, in tile-relative 32-bit arithmetic: counts the frames that
+ * start in [rel, rhi) and keeps the tile offsets of the first eight in four registers (16 bits
+ * each).  Anything that is not a plain run of complete frames inside one session - the session's
+ * bytes end here, a frame is incomplete, a length is bad - only sets `events`: that lane then goes
+ * through walk_subrange, which also does the per-session bookkeeping. */
+__device__ __forceinline__ uint32_t walk_count_fast(const uint8_t *tile, uint32_t rel, const uint32_t rhi,
+    const uint32_t rsend, uint32_t (&pk)[4], bool &events)
+{
+	uint32_t cnt = 0;
+	for (;;) {
+		if (rel == rsend) { events = true; break; }
+		if (rel >= rhi) break;
+		const uint32_t rem = rsend - rel;
+		if (rem < 4) { events = true; break; }
+		const int32_t len = (int32_t)sm_be32(tile, rel);
+		if (!len_ok(len) || rem < 4u + (uint32_t)len) { events = true; break; }
+		const uint32_t v = rel << ((cnt & 1u) * 16u);
+#pragma unroll
+		for (int j = 0; j < 4; ++j)
+			if ((cnt >> 1) == (uint32_t)j) pk[j] |= v;
+		cnt++;
+		rel += 4u + (uint32_t)len;
+	}
+	return cnt;
+}
+
 /* one BUF row */
 __device__ __forceinline__ void put_buf(const zkb_decoded &o, uint32_t row, uint32_t frame, uint64_t off, int32_t len)
 {
@@ -124,37 +150,56 @@ __device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, cons
 		const int32_t count = (int32_t)sm_be32(c.tile, vrel);
 		uint32_t cur = vrel + 4;
 		bool ok = true;
+		const uint64_t base = cs + 4;
+		const uint64_t want = count > 0 ? (uint64_t)count : 0u;
 		if (kind == VK_STR || kind == VK_STR_STAT) {
-			/* vector<ustring> (zk-buffer.js:334-337) */
-			for (int32_t k = 0; k < count; ++k) {
-				if (cur + 4 > end) { ok = false; break; }
-				const int32_t l = (int32_t)sm_be32(c.tile, cur);
-				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
-				if (cur + 4 + ul > end) { ok = false; break; }
-				put_buf(o, brow++, frame, cs + cur + 4, (int32_t)ul);
-				cur += 4 + ul;
+			/* vector<ustring> (zk-buffer.js:334-337).  An element's length is read even when fewer
+			 * than four bytes are left (the tile is zero padded): the end test below catches it. */
+			if (brow + want <= o.cap_buf) {
+				uint32_t *pf = o.buf_frame + brow; uint64_t *po = o.buf_off + brow; int32_t *pl = o.buf_len + brow;
+				int32_t k = 0;
+				for (; k < count; ++k) {
+					const int32_t l = (int32_t)sm_be32(c.tile, cur);
+					const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+					const uint32_t nxt = cur + 4 + ul;
+					if (nxt > end) break;
+					pf[k] = frame; po[k] = base + cur; pl[k] = (int32_t)ul;
+					cur = nxt;
+				}
+				ok = k >= count;
+			} else {
+				for (int32_t k = 0; k < count; ++k) {
+					if (cur + 4 > end) { ok = false; break; }
+					const int32_t l = (int32_t)sm_be32(c.tile, cur);
+					const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+					if (cur + 4 + ul > end) { ok = false; break; }
+					put_buf(o, brow++, frame, base + cur, (int32_t)ul);
+					cur += 4 + ul;
+				}
 			}
 		} else {
 			/* readACL (zk-buffer.js:372-382): count x { perms, scheme, id } */
+			const bool fits = brow + 2 * want <= o.cap_buf && arow + want <= o.cap_acl;
 			for (int32_t k = 0; k < count; ++k) {
-				if (cur + 4 > end) { ok = false; break; }
 				const int32_t perms = (int32_t)sm_be32(c.tile, cur);
-				cur += 4;
-				if (cur + 4 > end) { ok = false; break; }
-				const int32_t l0 = (int32_t)sm_be32(c.tile, cur);
+				const int32_t l0 = (int32_t)sm_be32(c.tile, cur + 4);
 				const uint32_t u0 = l0 > 0 ? (uint32_t)l0 : 0u;
-				if (cur + 4 + u0 > end) { ok = false; break; }
-				const uint32_t p0 = cur + 4;
-				cur += 4 + u0;
-				if (cur + 4 > end) { ok = false; break; }
-				const int32_t l1 = (int32_t)sm_be32(c.tile, cur);
+				const uint32_t c1 = cur + 8 + u0;                  /* length prefix of the id */
+				if (c1 + 4 > end) { ok = false; break; }
+				const int32_t l1 = (int32_t)sm_be32(c.tile, c1);
 				const uint32_t u1 = l1 > 0 ? (uint32_t)l1 : 0u;
-				if (cur + 4 + u1 > end) { ok = false; break; }
-				if (arow < o.cap_acl) { o.acl_frame[arow] = frame; o.acl_perms[arow] = perms; }
-				arow++;
-				put_buf(o, brow++, frame, cs + p0, (int32_t)u0);
-				put_buf(o, brow++, frame, cs + cur + 4, (int32_t)u1);
-				cur += 4 + u1;
+				if (c1 + 4 + u1 > end) { ok = false; break; }
+				if (fits) {
+					o.acl_frame[arow] = frame; o.acl_perms[arow] = perms;
+					o.buf_frame[brow] = frame; o.buf_off[brow] = base + cur + 4; o.buf_len[brow] = (int32_t)u0;
+					o.buf_frame[brow + 1] = frame; o.buf_off[brow + 1] = base + c1; o.buf_len[brow + 1] = (int32_t)u1;
+				} else {
+					if (arow < o.cap_acl) { o.acl_frame[arow] = frame; o.acl_perms[arow] = perms; }
+					put_buf(o, brow, frame, base + cur + 4, (int32_t)u0);
+					put_buf(o, brow + 1, frame, base + c1, (int32_t)u1);
+				}
+				arow++; brow += 2;
+				cur = c1 + 4 + u1;
 			}
 		}
 		if (ok) {
@@ -288,6 +333,106 @@ __device__ __forceinline__ bool direct_response(const uint8_t *t, const DecArgs 
 	    op == ZKB_OP_CLOSE_SESSION;
 }
 
+/* A GET_CHILDREN / GET_CHILDREN2 reply that reaches past the tile (10^4-10^5 children, config 4):
+ * header and child count are inside the tile, so the FRAMES row is written like any other; the
+ * children are walked by the whole warp once the chunk's other frames are done (long_children).
+ * Returns false for everything else, which the generic parser takes. */
+__device__ __forceinline__ bool direct_response_long(ChunkSm &c, const DecArgs &a, const uint32_t pr, const uint32_t size,
+    const uint32_t wlen, const uint32_t s, FrameCols &o)
+{
+	if (size < 20 || pr + 20 > wlen) return false;
+	const uint8_t *t = c.tile;
+	const int32_t xid = (int32_t)sm_be32(t, pr);
+	if (special_xid(xid) != ZKB_OP_NONE || !a.xt_ops) return false;
+	const int64_t idx = (int64_t)xid - (int64_t)__ldg(a.xt_base + s);
+	if (idx < 0 || idx >= (int64_t)__ldg(a.xt_count + s)) return false;
+	const int op = __ldg(a.xt_ops + __ldg(a.xt_off + s) + (uint64_t)idx);
+	if (op != ZKB_OP_GET_CHILDREN && op != ZKB_OP_GET_CHILDREN2) return false;
+	const int32_t err = (int32_t)sm_be32(t, pr + 12);
+	if (err != 0) return false;
+	const int32_t n = (int32_t)sm_be32(t, pr + 16);
+	o.xid = xid; o.err = 0; o.a1 = 0; o.a0 = n > 0 ? n : 0;
+	o.zxid = (int64_t)(((uint64_t)sm_be32(t, pr + 4) << 32) | (uint64_t)sm_be32(t, pr + 8));
+	o.meta = ZKB_ST_OK | ((uint32_t)(uint8_t)(int8_t)op << 8) | ((uint32_t)ZKB_KIND_RESPONSE << 16);
+	c.lp.n_buf = (uint32_t)o.a0; c.lp.n_stat = (op == ZKB_OP_GET_CHILDREN2) ? 1u : 0u; c.lp.n_acl = 0;
+	return true;
+}
+
+/* The children of such a reply: the warp stages the vector through its tile 8 KiB at a time; lane 0
+ * follows the length prefixes (a serial chain, but out of shared memory) and lists the elements it
+ * finds, then all lanes write the listed BUF rows side by side.  `phase` is the parity of the warp's
+ * mbarrier for its next use.  Returns false if the vector or the Stat behind it runs out of bytes. */
+__device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
+    const uint64_t foff, const uint32_t flen, const uint32_t frame, const uint32_t brow0, const uint32_t srow,
+    const bool with_stat, const uint32_t lane)
+{
+	const zkb_decoded &o = a.o;
+	const uint64_t fend = foff + 4 + (uint64_t)flen;
+	uint64_t pos = foff + 4 + 20;                         /* first element */
+	int64_t remaining = (int64_t)(int32_t)g_be32(a.bytes, foff + 4 + 16);
+	uint32_t row = brow0;
+	uint16_t *list = reinterpret_cast<uint16_t *>(c.vl);  /* the work-list area: the chunk's own frames are done */
+	const uint32_t cap = (uint32_t)(ZK_BM_BYTES / 2u) - 8u;
+	volatile uint32_t *note = reinterpret_cast<volatile uint32_t *>(&c.l_f);     /* lane 0 -> warp: elements listed */
+	bool ok = true;
+	while (remaining > 0 && ok) {
+		const uint64_t tb = pos & ~15ull;
+		const uint64_t avail = a.nbytes_pad - tb;
+		const uint32_t tlen = avail < (uint64_t)ZK_WIN ? (uint32_t)avail : ZK_WIN;
+		__syncwarp();
+		if (lane == 0) {
+			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+			mbar_expect_tx(bar, tlen);
+			bulk_g2s(c.tile, a.bytes + tb, tlen, bar);
+		}
+		__syncwarp();
+		mbar_wait(bar, phase);
+		phase ^= 1u;
+		uint32_t n = 0;
+		if (lane == 0) {
+			uint32_t rel = (uint32_t)(pos - tb);
+			uint64_t p = pos;
+			while (remaining > 0 && rel + 4 <= tlen && n < cap) {
+				const int32_t l = (int32_t)sm_be32(c.tile, rel);
+				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+				if (p + 4 + ul > fend) { ok = false; break; }
+				list[n++] = (uint16_t)rel;
+				rel += 4 + ul; p += 4 + (uint64_t)ul;
+				remaining--;
+			}
+			if (ok && n == 0 && remaining > 0) ok = false;     /* fewer than 4 bytes of the batch are left */
+			pos = p;
+			*note = n;
+		}
+		__syncwarp();
+		n = *note;
+		pos = __shfl_sync(0xffffffffu, pos, 0);
+		remaining = __shfl_sync(0xffffffffu, remaining, 0);
+		ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
+		for (uint32_t i = lane; i < n; i += 32) {
+			const uint32_t rel = list[i];
+			const int32_t l = (int32_t)sm_be32(c.tile, rel);
+			put_buf(o, row + i, frame, tb + rel + 4, l > 0 ? l : 0);
+		}
+		row += n;
+	}
+	if (ok && with_stat) {
+		if (pos + 68 > fend) ok = false;
+		else if (lane == 0 && srow < o.cap_stat) {
+			const uint8_t *g = a.bytes;
+#define G64(q) ((int64_t)(((uint64_t)g_be32(g, (q)) << 32) | (uint64_t)g_be32(g, (q) + 4)))
+			o.stat_frame[srow] = frame;
+			o.czxid[srow] = G64(pos); o.mzxid[srow] = G64(pos + 8); o.ctime[srow] = G64(pos + 16); o.mtime[srow] = G64(pos + 24);
+			o.version[srow] = (int32_t)g_be32(g, pos + 32); o.cversion[srow] = (int32_t)g_be32(g, pos + 36);
+			o.aversion[srow] = (int32_t)g_be32(g, pos + 40); o.ephemeralOwner[srow] = G64(pos + 44);
+			o.dataLength[srow] = (int32_t)g_be32(g, pos + 52); o.numChildren[srow] = (int32_t)g_be32(g, pos + 56);
+			o.pzxid[srow] = G64(pos + 60);
+#undef G64
+		}
+	}
+	return ok;
+}
+
 /* Everything one warp does for one 8 KiB chunk.  REDO == false: first rows from the splitter's
  * prediction (a.g_rbase), verified; REDO == true: first rows from the scan over the chunks' real
  * counts (a.c_base), chunks that need the exact body are skipped (they have their own launch). */
@@ -307,6 +452,7 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 		mbar_expect_tx(bar, wlen);
 		bulk_g2s(c.tile, a.bytes + cs, wlen, bar);
 		*reinterpret_cast<uint4 *>(c.tile + wlen) = make_uint4(0, 0, 0, 0);
+		c.have_long = 0;
 	}
 	Rd rd;
 	rd.sm = c.tile; rd.lo = cs; rd.wlen = wlen; rd.g = a.bytes;
@@ -349,9 +495,11 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 		const uint16_t v = a.g_sub[((size_t)a.g_sel[g] * a.n_gran + g) * subs + (uint32_t)((lo - gstart) >> 8)];
 		if (v != 0xFFFFu) entry = gstart + v;
 	}
-	/* session the entry lies in: jl = boundaries sess_off[sf + l], l < 32, strictly below it */
-	uint32_t es = 0; uint64_t esend = 0; bool e_start = false;
-	{
+	const bool one_session = cont && !(boff0 < ce || (last && sf < a.nsess));   /* no session starts inside */
+	/* session the entry lies in */
+	uint32_t es = sf - 1; uint64_t esend = boff0; bool e_start = false;
+	if (!one_session) {
+		/* jl = boundaries sess_off[sf + l], l < 32, strictly below the entry */
 		const uint64_t e = (entry != ZK_NONE) ? entry : 0;
 		uint32_t jl = 0;
 #pragma unroll
@@ -384,10 +532,21 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 	__syncwarp();
 	mbar_wait(bar, 0);
 
-	/* ---- frame starts: count per lane, prefix over lanes ---- */
-	const uint32_t mycnt = walk_subrange<false>(a, c, cs, hi, entry, es, esend, 0, 0, false, 0, false);
+	/* ---- frame starts: count per lane, prefix over lanes.  A lane whose sub-range is a plain run of
+	 * frames keeps their offsets in registers; the others (a session ends or starts there, a bad or
+	 * incomplete frame, more than eight frames) walk again below, with the bookkeeping ---- */
+	uint32_t pk[4] = { 0u, 0u, 0u, 0u };
+	bool events = e_start;
+	uint32_t mycnt = 0;
+	if (entry != ZK_NONE) {
+		const uint64_t d = esend - cs;
+		const uint32_t rsend = d > 0x7fffffffull ? 0x7fffffffu : (uint32_t)d;
+		mycnt = walk_count_fast(c.tile, (uint32_t)(entry - cs), (uint32_t)(hi - cs), rsend, pk, events);
+		if (events) mycnt = walk_subrange<false>(a, c, cs, hi, entry, es, esend, 0, 0, false, 0, false);
+	}
 	const uint32_t lbase = warp_incl_scan(mycnt, lane) - mycnt;
 	if (lane == 31 && lbase + mycnt != nfr) atomicOr(&a.ctrl->error, ZK_DERR_COUNT);
+	const bool simple = nfr <= ZK_FREL_CAP;      /* one window: offsets can come straight from the registers */
 	if (last && lane == 0) {
 		/* empty sessions at the very end of the batch start at nbytes, in no sub-range */
 		for (uint32_t sx = a.nsess; sx > 0 && __ldg(a.sess_off + sx - 1) == a.nbytes; --sx) {
@@ -396,21 +555,22 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 			a.o.sess_first_frame[sx - 1] = (uint32_t)a.n_frames;
 		}
 	}
-	const bool one_session = cont && !(boff0 < ce || (last && sf < a.nsess));   /* no session starts inside */
-
 	uint32_t rs = 0, rb = 0, ra = 0;       /* rows of the chunk placed so far (stat, buf, acl) */
 	uint32_t nv = 0;                       /* vectors set aside */
 	bool good = true;
 	uint32_t n_slow = 0;
-	Parsed lp;                             /* the chunk's long frame (reaches past the tile), if this lane has it */
-	uint64_t l_foff = 0; int32_t l_flen = 0; uint32_t l_f = 0;
-	lp.n_stat = lp.n_buf = lp.n_acl = 0;
 
 	uint32_t wlo = 0;
 	do {
 		/* ---- tile offsets of frames wlo .. wlo + ZK_FREL_CAP - 1; the first window also does the
 		 * per-session bookkeeping ---- */
-		walk_subrange<true>(a, c, cs, hi, entry, es, esend, wlo, lbase, wlo == 0, f0 + lbase, e_start);
+		if (simple && !events && mycnt <= 8) {
+#pragma unroll
+			for (int i = 0; i < 8; ++i)
+				if ((uint32_t)i < mycnt) c.frel[lbase + i] = (uint16_t)(pk[i >> 1] >> ((i & 1) * 16));
+		} else {
+			walk_subrange<true>(a, c, cs, hi, entry, es, esend, wlo, lbase, wlo == 0, f0 + lbase, e_start);
+		}
 		__syncwarp();
 		const uint32_t wend = (nfr - wlo < ZK_FREL_CAP) ? nfr : wlo + ZK_FREL_CAP;
 		for (uint32_t k0 = wlo; k0 < wend; k0 += 32) {
@@ -468,6 +628,11 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 				if (inwin && idx >= hs)
 					done = server ? direct_request(c.tile, rel + 4, (uint32_t)flen, o, fr)
 					              : direct_response(c.tile, a, rel + 4, (uint32_t)flen, s, o, fr);
+				if (!done && !inwin && !server && idx >= hs &&
+				    direct_response_long(c, a, rel + 4, (uint32_t)flen, wlen, s, o)) {
+					done = true;
+					c.l_foff = foff; c.l_flen = flen; c.l_f = f; c.have_long = 2;
+				}
 				if (!done) {
 					/* handshake frames, malformed frames, frames longer than the tile: exact reader */
 					Parsed p;
@@ -477,7 +642,7 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 					fr.nst = fr.nbf = fr.nac = 0; fr.b0 = fr.b1 = fr.st = 0; fr.vrel = 0; fr.vkind = 0;
 					if (p.n_stat | p.n_buf | p.n_acl) {
 						if (inwin) { fr.slow = 1; fr.nst = p.n_stat; fr.nbf = p.n_buf; fr.nac = p.n_acl; }
-						else { fr.slow = 2; lp = p; l_foff = foff; l_flen = flen; l_f = f; }
+						else { fr.slow = 2; c.lp = p; c.l_foff = foff; c.l_flen = flen; c.l_f = f; c.have_long = 1; }
 					}
 				}
 				a.o.meta[f] = o.meta;
@@ -531,9 +696,21 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 	if (lane == 0 && n_slow) atomicAdd(&a.ctrl->n_slow, (unsigned long long)n_slow);
 
 	/* the long frame's rows come last: it is the chunk's last frame */
-	const uint32_t ts = rs + warp_sum(lp.n_stat), tb = rb + warp_sum(lp.n_buf), ta = ra + warp_sum(lp.n_acl);
-	if (lp.n_stat | lp.n_buf | lp.n_acl)
-		emit_side(rd, a, l_foff, l_flen, lp, l_f, e0 + rs, e1 + rb, e2 + ra);
+	__syncwarp();
+	uint32_t ts = rs, tb = rb, ta = ra;
+	const uint32_t have_long = c.have_long;
+	if (have_long) {
+		ts += c.lp.n_stat; tb += c.lp.n_buf; ta += c.lp.n_acl;
+		if (have_long == 2) {
+			const uint64_t lf = c.l_foff; const uint32_t ll = (uint32_t)c.l_flen, lfr = c.l_f;
+			const bool st = c.lp.n_stat != 0;
+			__syncwarp();
+			good = long_children(a, c, bar, 1u, lf, ll, lfr, e1 + rb, e0 + rs, st, lane) && good;
+		} else if (lane == 0) {
+			const Parsed p = c.lp;
+			emit_side(rd, a, c.l_foff, c.l_flen, p, c.l_f, e0 + rs, e1 + rb, e2 + ra);
+		}
+	}
 	if (!REDO && lane == 0) {
 		/* what the chunk really has (a frame that broke its promise owns no rows: the exact body
 		 * counts them when the chunk is done again) */
