@@ -199,6 +199,9 @@ __device__ bool chain_plausible(const uint8_t *bytes, uint64_t q, uint64_t send,
 #ifndef ZK_GUESS_HOPS
 #define ZK_GUESS_HOPS 3
 #endif
+#ifndef ZK_GUESS_SPAN
+#define ZK_GUESS_SPAN 8192u
+#endif
 #ifndef ZK_GUESS_HOPS_SERVER
 #define ZK_GUESS_HOPS_SERVER 1   /* requests: the local test already checks the path */
 #endif
@@ -258,8 +261,7 @@ __device__ bool guess_local(const GuessCtx &g, uint64_t p)
  * 16 positions of a load at once, where a header could start at all: a request has the three high
  * bytes of a small opcode eight bytes in, a reply the four bytes of err 0 - or the three 0xff of a
  * negative err - sixteen bytes in.  Only those few positions get the local test, and what passes it
- * is checked by following the chain; the far (DRAM-latency) checks are made after each 128-byte
- * segment so the lanes of a warp, which scan different granules, issue them together.  (Requests
+ * is checked by following the chain.  (Requests
  * with a negative opcode are not proposed: a granule that starts with one takes the next frame and is
  * put right by the fix-up.) */
 __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uint64_t ge, uint64_t send)
@@ -268,6 +270,11 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 	g.bytes = a.bytes;
 	g.server = a.sess_flags && (a.sess_flags[s] & ZKB_SESS_SERVER);
 	g.lim = ge < send ? ge : send;
+	/* build knob: a guess may give up after ZK_GUESS_SPAN bytes (a frame that starts further on is then
+	 * found by the fix-up pass).  Measured on config 4 with 2 KiB: the scan gets 4 x cheaper, but every
+	 * megabyte frame that ends deep inside a granule costs a fix-up round, and those rounds run one after
+	 * the other along a session - slower overall; the default scans the whole granule. */
+	if (g.lim > gs + ZK_GUESS_SPAN) g.lim = gs + ZK_GUESS_SPAN;
 	g.send = send;
 	g.xw.on = a.xt_ops != NULL && !g.server;
 	g.xw.base = g.xw.on ? (int64_t)__ldg(a.xt_base + s) : 0;
@@ -280,47 +287,44 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 	if (gs + 32 <= padend) v1 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs + 16));
 	uint32_t z0 = mask16_zero(v0), z1 = mask16_zero(v1);
 	uint32_t f0 = g.server ? 0u : mask16_ff(v0), f1 = g.server ? 0u : mask16_ff(v1);
-	for (uint64_t seg = gs; seg < g.lim; seg += 128) {
-		/* phase 1: masks only, the lanes of a warp stay in step */
-		uint64_t cand_lo = 0, cand_hi = 0;
+	uint64_t blk = gs;            /* next 16 bytes to scan */
+	uint64_t cand = 0, cbase = 0; /* positions of a 64-byte group that passed the masks and are not tested yet */
+	for (;;) {
+		/* scan on, 64 bytes at a time, until this lane has something to test; the lanes of a warp
+		 * (which scan different granules) meet again below, so the tests - the local one and the far,
+		 * DRAM-latency ones - run for all of them together */
+		while (!cand && blk < g.lim) {
+			cbase = blk;
 #pragma unroll 1
-		for (int q = 0; q < 8; ++q) {
-			const uint64_t blk = seg + 16 * q;
-			v2 = zero4;
-			if (blk + 48 <= padend) v2 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + blk + 32));
-			const uint32_t z2 = mask16_zero(v2);
-			const uint32_t f2 = g.server ? 0u : mask16_ff(v2);
-			if (blk < g.lim) {
-				const uint64_t Z = (uint64_t)z0 | ((uint64_t)z1 << 16) | ((uint64_t)z2 << 32);
-				uint32_t c = mask16_le1(v0);
-				if (g.server) {
-					c &= (uint32_t)(Z >> 8) & (uint32_t)(Z >> 9) & (uint32_t)(Z >> 10);
-				} else {
-					const uint64_t F = (uint64_t)f0 | ((uint64_t)f1 << 16) | ((uint64_t)f2 << 32);
-					const uint32_t e0 = (uint32_t)(Z >> 16) & (uint32_t)(Z >> 17) & (uint32_t)(Z >> 18) & (uint32_t)(Z >> 19);
-					const uint32_t en = (uint32_t)(F >> 16) & (uint32_t)(F >> 17) & (uint32_t)(F >> 18);
-					c &= (e0 | en);
+			for (int q = 0; q < 4; ++q, blk += 16) {
+				v2 = zero4;
+				if (blk + 48 <= padend) v2 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + blk + 32));
+				const uint32_t z2 = mask16_zero(v2);
+				const uint32_t f2 = g.server ? 0u : mask16_ff(v2);
+				if (blk < g.lim) {
+					const uint64_t Z = (uint64_t)z0 | ((uint64_t)z1 << 16) | ((uint64_t)z2 << 32);
+					uint32_t c = mask16_le1(v0);
+					if (g.server) {
+						c &= (uint32_t)(Z >> 8) & (uint32_t)(Z >> 9) & (uint32_t)(Z >> 10);
+					} else {
+						const uint64_t F = (uint64_t)f0 | ((uint64_t)f1 << 16) | ((uint64_t)f2 << 32);
+						const uint32_t e0 = (uint32_t)(Z >> 16) & (uint32_t)(Z >> 17) & (uint32_t)(Z >> 18) & (uint32_t)(Z >> 19);
+						const uint32_t en = (uint32_t)(F >> 16) & (uint32_t)(F >> 17) & (uint32_t)(F >> 18);
+						c &= (e0 | en);
+					}
+					cand |= (uint64_t)(c & 0xffffu) << (16 * q);
 				}
-				c &= 0xffffu;
-				if (q < 4) cand_lo |= (uint64_t)c << (16 * q);
-				else cand_hi |= (uint64_t)c << (16 * (q - 4));
-			}
-			v0 = v1; v1 = v2; z0 = z1; z1 = z2; f0 = f1; f1 = f2;
-		}
-		/* phase 2: local test, then the far checks, candidate by candidate in stream order */
-#pragma unroll 1
-		for (int half = 0; half < 2; ++half) {
-			uint64_t cand = half ? cand_hi : cand_lo;
-			while (cand) {
-				const int k = __ffsll((long long)cand) - 1;
-				cand &= cand - 1;
-				const uint64_t p = seg + 64 * half + (uint64_t)k;
-				if (!guess_local(g, p)) continue;
-				const int32_t len = (int32_t)g_be32(a.bytes, p);
-				if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS, g.xw))
-					return p;
+				v0 = v1; v1 = v2; z0 = z1; z1 = z2; f0 = f1; f1 = f2;
 			}
 		}
+		if (!cand) break;
+		const int k = __ffsll((long long)cand) - 1;
+		cand &= cand - 1;
+		const uint64_t p = cbase + (uint64_t)k;
+		if (!guess_local(g, p)) continue;
+		const int32_t len = (int32_t)g_be32(a.bytes, p);
+		if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS, g.xw))
+			return p;
 	}
 	return ZK_NONE;
 }
@@ -873,6 +877,9 @@ struct DecArgs {
 	uint32_t        n_chunks;
 	uint64_t        n_frames;
 	zkb_decoded     o;
+	const uint4    *meta0;        /* [n_chunks + 1] { first frame, first frame of the session the chunk starts in, first
+	                                 session starting at or after the chunk, bytes to that session's start (saturated) } */
+	const uint4    *meta1;        /* [n_chunks + 1] predicted first { stat, buf, acl } row of the chunk */
 	uint4          *c_rows;       /* [n_chunks] { needs the exact body, stat rows, buf rows, acl rows } the chunk really has */
 	uint4          *c_base;       /* [n_chunks] exclusive prefix of c_rows (redo passes) */
 	uint32_t        chunk0;       /* first chunk of this launch (a redo covers only the tail of a batch) */
@@ -2052,6 +2059,31 @@ __device__ __forceinline__ void decode_chunk_exact(const DecArgs &a, ChunkSm &c,
 #endif
 }
 
+/* Everything the decode kernel wants to know about a chunk before it looks at the bytes, gathered
+ * from the splitter's per-granule tables into two 16-byte records per chunk, so that a decode warp
+ * gets it with one round of independent loads instead of a chain of dependent ones. */
+__global__ void k_chunk_meta(DecArgs a, uint4 *meta0, uint4 *meta1)
+{
+	const uint32_t chunk = blockIdx.x * blockDim.x + threadIdx.x;
+	if (chunk > a.n_chunks) return;
+	if (chunk == a.n_chunks) {
+		meta0[chunk] = make_uint4((uint32_t)a.n_frames, 0u, a.nsess, 0u);
+		meta1[chunk] = a.g_rbase[a.n_gran];
+		return;
+	}
+	const uint32_t g0 = chunk << (ZK_CHUNK_LOG2 - a.glog2);
+	const uint64_t cs = (uint64_t)chunk << ZK_CHUNK_LOG2;
+	const uint32_t sf = a.g_sf[g0];
+	const uint64_t d = __ldg(a.sess_off + sf) - cs;
+	uint32_t sfirst = 0;
+	if (d != 0) {
+		const uint32_t src = a.g_ssrc[g0];
+		if (src) sfirst = a.g_base[src - 1] + a.g_openlocal[(size_t)a.g_sel[src - 1] * a.n_gran + (src - 1)];
+	}
+	meta0[chunk] = make_uint4(a.g_base[g0], sfirst, sf, d > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)d);
+	meta1[chunk] = a.g_rbase[g0];
+}
+
 #include "zk_decode_direct.cuh"
 
 /* One CTA = ZK_DEC_WARPS warps = that many consecutive chunks, chunk index from blockIdx.  The
@@ -2187,7 +2219,7 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 }
 
 struct ScratchLayout {
-	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, c_rows, c_base, total;
+	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, c_rows, c_base, meta0, meta1, total;
 	uint32_t glog2, n_gran, n_chunks, n_blk;
 };
 
@@ -2217,6 +2249,8 @@ static ScratchLayout zk_layout(uint64_t nbytes)
 	L.blk = o;       o += zk_align_up((size_t)(L.n_blk + 1) * sizeof (ScanVal), 256);
 	L.c_rows = o;    o += zk_align_up((size_t)L.n_chunks * 16, 256);
 	L.c_base = o;    o += zk_align_up((size_t)L.n_chunks * 16, 256);
+	L.meta0 = o;     o += zk_align_up((size_t)(L.n_chunks + 1) * 16, 256);
+	L.meta1 = o;     o += zk_align_up((size_t)(L.n_chunks + 1) * 16, 256);
 	L.total = o;
 	return L;
 }
@@ -2409,6 +2443,12 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	const unsigned dec_blocks = (L.n_chunks + ZK_DEC_WARPS - 1) / ZK_DEC_WARPS;
 	const unsigned dec_threads = ZK_DEC_WARPS * 32;
 	ZK_EV(ctx, 4);
+	{
+		uint4 *m0 = (uint4 *)(S + L.meta0), *m1 = (uint4 *)(S + L.meta1);
+		k_chunk_meta<<<(L.n_chunks + 1 + 255) / 256, 256, 0, ctx->stream>>>(da, m0, m1);
+		LAUNCH_CHECK(ctx);
+		da.meta0 = m0; da.meta1 = m1;
+	}
 	bool redo = ctx->no_predict != 0;
 	unsigned long long slow_first = 0;
 	bool have_slow = false;

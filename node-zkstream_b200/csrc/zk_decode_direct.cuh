@@ -358,10 +358,59 @@ __device__ __forceinline__ bool direct_response_long(ChunkSm &c, const DecArgs &
 	return true;
 }
 
-/* The children of such a reply: the warp stages the vector through its tile 8 KiB at a time; lane 0
- * follows the length prefixes (a serial chain, but out of shared memory) and lists the elements it
- * finds, then all lanes write the listed BUF rows side by side.  `phase` is the parity of the warp's
- * mbarrier for its next use.  Returns false if the vector or the Stat behind it runs out of bytes. */
+/* ---- children vectors longer than the tile ------------------------------------------------
+ * The warp stages the vector through its tile 8 KiB at a time.  Inside a tile the elements are a
+ * chain of length prefixes like the frames of a stream, and they are found the same way: every lane
+ * takes a 280-byte sub-range, guesses where the chain stands in it (the first position that looks
+ * like the prefix of a short, non-empty string and from which three more such prefixes follow),
+ * and walks to the end of its sub-range; then the lanes compare notes from the left - the chain's
+ * true entry into the tile is known - and a lane whose guess is not where its left neighbour's
+ * walk ended walks again from there.  A wrong guess costs a repair round, never a wrong row. */
+#define ZK_LSUB 280u
+static_assert(ZK_LSUB * 32u >= ZK_WIN, "the 32 sub-ranges must cover the tile");
+
+/* elements that start in [p, hi): count them (EMIT == false) or write their BUF rows (EMIT == true,
+ * at most `maxn`); returns where the chain stands afterwards.  A prefix that cannot be read inside
+ * the tile, or an element that runs past the frame (`vlim`), ends the walk. */
+template <bool EMIT>
+__device__ __forceinline__ uint32_t walk_elems(const uint8_t *tile, uint32_t p, const uint32_t hi, const uint32_t tlen,
+    const uint32_t vlim, uint32_t &n, const uint32_t maxn, const zkb_decoded &o, uint32_t row, const uint32_t frame,
+    const uint64_t tb)
+{
+	n = 0;
+	while (p < hi && p + 4 <= tlen && (!EMIT || n < maxn)) {
+		const int32_t l = (int32_t)sm_be32(tile, p);
+		const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+		if (p + 4 + ul > vlim) break;
+		if (EMIT) put_buf(o, row++, frame, tb + p + 4, (int32_t)ul);
+		n++;
+		p += 4 + ul;
+	}
+	return p;
+}
+
+/* first position in [lo, hi) that looks like an element prefix (see above), or 0xFFFFFFFF */
+__device__ __forceinline__ uint32_t guess_elem(const uint8_t *tile, const uint32_t lo, const uint32_t hi, const uint32_t tlen)
+{
+	for (uint32_t q = lo; q < hi && q + 4 <= tlen; ++q) {
+		const uint32_t w = sm_be32(tile, q);
+		if (w == 0 || w > 255u) continue;
+		uint32_t r = q + 4 + w;
+		bool good = true;
+#pragma unroll 1
+		for (int h = 0; h < 3 && good; ++h) {
+			if (r + 4 > tlen) break;
+			const uint32_t w2 = sm_be32(tile, r);
+			if (w2 > 255u) good = false;
+			r += 4 + w2;
+		}
+		if (good) return q;
+	}
+	return 0xFFFFFFFFu;
+}
+
+/* `phase` is the parity of the warp's mbarrier for its next use.  Returns false if the vector or
+ * the Stat behind it runs out of bytes. */
 __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
     const uint64_t foff, const uint32_t flen, const uint32_t frame, const uint32_t brow0, const uint32_t srow,
     const bool with_stat, const uint32_t lane)
@@ -371,14 +420,12 @@ __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint
 	uint64_t pos = foff + 4 + 20;                         /* first element */
 	int64_t remaining = (int64_t)(int32_t)g_be32(a.bytes, foff + 4 + 16);
 	uint32_t row = brow0;
-	uint16_t *list = reinterpret_cast<uint16_t *>(c.vl);  /* the work-list area: the chunk's own frames are done */
-	const uint32_t cap = (uint32_t)(ZK_BM_BYTES / 2u) - 8u;
-	volatile uint32_t *note = reinterpret_cast<volatile uint32_t *>(&c.l_f);     /* lane 0 -> warp: elements listed */
 	bool ok = true;
 	while (remaining > 0 && ok) {
 		const uint64_t tb = pos & ~15ull;
 		const uint64_t avail = a.nbytes_pad - tb;
 		const uint32_t tlen = avail < (uint64_t)ZK_WIN ? (uint32_t)avail : ZK_WIN;
+		const uint32_t vlim = fend - tb > 0x40000000ull ? 0x40000000u : (uint32_t)(fend - tb);
 		__syncwarp();
 		if (lane == 0) {
 			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -388,33 +435,49 @@ __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint
 		__syncwarp();
 		mbar_wait(bar, phase);
 		phase ^= 1u;
-		uint32_t n = 0;
-		if (lane == 0) {
-			uint32_t rel = (uint32_t)(pos - tb);
-			uint64_t p = pos;
-			while (remaining > 0 && rel + 4 <= tlen && n < cap) {
-				const int32_t l = (int32_t)sm_be32(c.tile, rel);
-				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
-				if (p + 4 + ul > fend) { ok = false; break; }
-				list[n++] = (uint16_t)rel;
-				rel += 4 + ul; p += 4 + (uint64_t)ul;
-				remaining--;
+		const uint32_t start = (uint32_t)(pos - tb);
+		const uint32_t lo = lane * ZK_LSUB;
+		const uint32_t hi = (lo + ZK_LSUB < tlen) ? lo + ZK_LSUB : tlen;
+		/* first try: the lane that holds the chain's entry walks from it, the lanes after it guess */
+		uint32_t in, out, n = 0;
+		if (hi <= start || lo >= tlen) { in = out = start; }
+		else {
+			in = (lo <= start) ? start : guess_elem(c.tile, lo, hi, tlen);
+			out = (in == 0xFFFFFFFFu) ? in : walk_elems<false>(c.tile, in, hi, tlen, vlim, n, 0, o, 0, 0, 0);
+		}
+		/* repair from the left until every lane starts where its neighbour ended */
+		for (;;) {
+			uint32_t prev = __shfl_up_sync(0xffffffffu, out, 1);
+			if (lane == 0) prev = start;
+			const bool active = !(hi <= start || lo >= tlen);
+			const uint32_t wrong = __ballot_sync(0xffffffffu, active && in != prev);
+			if (!wrong) break;
+			if (lane == (uint32_t)(__ffs(wrong) - 1)) {
+				in = prev;
+				out = walk_elems<false>(c.tile, in, hi, tlen, vlim, n, 0, o, 0, 0, 0);
 			}
-			if (ok && n == 0 && remaining > 0) ok = false;     /* fewer than 4 bytes of the batch are left */
-			pos = p;
-			*note = n;
 		}
-		__syncwarp();
-		n = *note;
-		pos = __shfl_sync(0xffffffffu, pos, 0);
-		remaining = __shfl_sync(0xffffffffu, remaining, 0);
-		ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
-		for (uint32_t i = lane; i < n; i += 32) {
-			const uint32_t rel = list[i];
-			const int32_t l = (int32_t)sm_be32(c.tile, rel);
-			put_buf(o, row + i, frame, tb + rel + 4, l > 0 ? l : 0);
+		/* rows: lane l's elements follow those of the lanes before it */
+		const uint32_t inc = warp_incl_scan(n, lane);
+		const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+		const uint32_t before = inc - n;
+		const uint32_t left = remaining > (int64_t)0x7fffffff ? 0x7fffffffu : (uint32_t)remaining;
+		const uint32_t mine = before >= left ? 0u : (left - before < n ? left - before : n);
+		uint32_t wrote = 0;
+		const uint32_t endp = walk_elems<true>(c.tile, in, hi, tlen, vlim, wrote, mine, o, row + before, frame, tb);
+		/* where the chain stands after the tile: what the last lane that has bytes says */
+		const uint32_t act = __ballot_sync(0xffffffffu, lo < tlen);
+		uint32_t last_out = __shfl_sync(0xffffffffu, out, 31 - __clz((int)act));
+		if (total >= left) {
+			/* the vector ends in this tile: the lane that wrote its last element knows where */
+			const uint32_t who = __ballot_sync(0xffffffffu, mine > 0 && before + mine == left);
+			last_out = __shfl_sync(0xffffffffu, endp, who ? __ffs(who) - 1 : 0);
+			row += left; remaining = 0;
+		} else {
+			if (total == 0) ok = false;              /* no readable element where one must be */
+			row += total; remaining -= total;
 		}
-		row += n;
+		pos = tb + last_out;
 	}
 	if (ok && with_stat) {
 		if (pos + 68 > fend) ok = false;
@@ -457,34 +520,22 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 	Rd rd;
 	rd.sm = c.tile; rd.lo = cs; rd.wlen = wlen; rd.g = a.bytes;
 
-	const uint32_t gsh = ZK_CHUNK_LOG2 - a.glog2;
-	const uint32_t g0 = chunk << gsh, g1 = (chunk + 1) << gsh;
-	const uint32_t f0 = a.g_base[g0];
-	const uint32_t f1 = (g1 < a.n_gran) ? a.g_base[g1] : (uint32_t)a.n_frames;
-	const uint32_t nfr = f1 - f0;
-	const bool last = (chunk == a.n_chunks - 1);
-	const uint64_t ce = last ? a.nbytes : cs + ZK_CHUNK;
-	const uint32_t sf = a.g_sf[g0];                  /* first session starting at or after cs */
-	uint64_t boff = ZK_NONE;                         /* boff[l] = sess_off[sf + l] */
-	if (sf + lane <= a.nsess) boff = __ldg(a.sess_off + sf + lane);
-	const uint64_t boff0 = __shfl_sync(0xffffffffu, boff, 0);
-	const bool cont = (boff0 != cs);                 /* the chunk starts inside session sf-1 */
-	uint32_t sfirst = 0;                             /* first frame (batch row) of that session */
-	if (cont) {
-		const uint32_t src = a.g_ssrc[g0];
-		if (src) sfirst = a.g_base[src - 1] + a.g_openlocal[(size_t)a.g_sel[src - 1] * a.n_gran + (src - 1)];
-	}
-	/* first rows of the chunk */
-	uint32_t e0, e1, e2, p0 = 0, p1 = 0, p2 = 0;
+	/* the chunk's records and this lane's sub-range entry: independent loads, one round trip */
+	const uint4 m0 = a.meta0[chunk];
+	const uint32_t f1 = a.meta0[chunk + 1].x;
+	uint32_t e0, e1, e2, p0 = 0, p1 = 0, p2 = 0;     /* first rows of the chunk; rows the splitter predicted for it */
 	if (REDO) {
 		const uint4 cb = a.c_base[chunk];
 		e0 = cb.y; e1 = cb.z; e2 = cb.w;
 	} else {
-		const uint4 rb0 = a.g_rbase[g0], rb1 = a.g_rbase[g1 < a.n_gran ? g1 : a.n_gran];
+		const uint4 rb0 = a.meta1[chunk], rb1 = a.meta1[chunk + 1];
 		e0 = rb0.x; e1 = rb0.y; e2 = rb0.z;
 		p0 = rb1.x - rb0.x; p1 = rb1.y - rb0.y; p2 = rb1.z - rb0.z;
 	}
-	/* where the chain stands inside this lane's 256-byte sub-range, from the splitter */
+	const bool last = (chunk == a.n_chunks - 1);
+	const uint64_t ce = last ? a.nbytes : cs + ZK_CHUNK;
+	/* where the chain stands inside this lane's 256-byte sub-range, from the splitter (both recorded
+	 * walks are fetched, the selection picks one) */
 	const uint64_t lo = cs + 256u * lane;
 	const uint64_t hi = (lo + 256 < ce) ? lo + 256 : ce;
 	uint64_t entry = ZK_NONE;
@@ -492,10 +543,20 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 		const uint32_t g = (uint32_t)(lo >> a.glog2);
 		const uint64_t gstart = (uint64_t)g << a.glog2;
 		const uint32_t subs = 1u << (a.glog2 - 8);
-		const uint16_t v = a.g_sub[((size_t)a.g_sel[g] * a.n_gran + g) * subs + (uint32_t)((lo - gstart) >> 8)];
+		const uint32_t si = (uint32_t)((lo - gstart) >> 8);
+		const uint16_t v0 = a.g_sub[(size_t)g * subs + si];
+		const uint16_t v1 = a.g_sub[((size_t)a.n_gran + g) * subs + si];
+		const uint16_t v = a.g_sel[g] ? v1 : v0;
 		if (v != 0xFFFFu) entry = gstart + v;
 	}
-	const bool one_session = cont && !(boff0 < ce || (last && sf < a.nsess));   /* no session starts inside */
+	const uint32_t f0 = m0.x, sfirst = m0.y, sf = m0.z;
+	const uint32_t nfr = f1 - f0;
+	const bool cont = (m0.w != 0);                   /* the chunk starts inside session sf-1 */
+	/* no session starts inside the chunk: then nothing but the records above is needed */
+	const bool one_session = cont && !((uint64_t)m0.w < ce - cs || (last && sf < a.nsess));
+	uint64_t boff = ZK_NONE;                         /* boff[l] = sess_off[sf + l] */
+	if (!one_session || m0.w == 0xFFFFFFFFu) { if (sf + lane <= a.nsess) boff = __ldg(a.sess_off + sf + lane); }
+	const uint64_t boff0 = (one_session && m0.w != 0xFFFFFFFFu) ? cs + m0.w : __shfl_sync(0xffffffffu, boff, 0);
 	/* session the entry lies in */
 	uint32_t es = sf - 1; uint64_t esend = boff0; bool e_start = false;
 	if (!one_session) {

@@ -394,3 +394,70 @@ def test_partial_redo_after_a_mispredicted_chunk(ctx, oracle, synth, zk, where):
     assert ctx.row_mispredicts == before + 1
     assert int(o.status[f]) == 1                               # the damaged frame is BAD_DECODE, everything else as before
     assert ctx.last_slow_frames >= 1
+
+
+def test_long_children_vectors_adversarial(ctx, oracle, synth):
+    """GET_CHILDREN / GET_CHILDREN2 replies longer than the decode tile: their children are found by
+    lanes that guess element boundaries inside 280-byte sub-ranges and repair each other from the
+    left.  Names built to mislead the guess (runs of zero bytes, empty names, names longer than 255
+    bytes, one name longer than a whole tile, byte patterns that look like prefixes), vectors that end
+    right at tile and sub-range boundaries, a count that lies in either direction, and ordinary frames
+    before and after - every row must still be the oracle's."""
+    import random
+    import struct
+    rng = random.Random(99)
+
+    def kids_frame(xid, names, op, count=None, stat=True):
+        body = synth.resp_header(xid, 7 + xid, 0) + synth.be32(len(names) if count is None else count)
+        body += b"".join(struct.pack(">i", len(n) if n or rng.random() < 0.5 else -1) + n for n in names)
+        if stat:
+            body += synth.stat_bytes(rng, 0, len(names))
+        return synth.frame(body)
+
+    def names_plain(n):
+        return [b"n%07d" % k + bytes(rng.randrange(0, 16)) for k in range(n)]
+
+    def names_nasty(n):
+        out = []
+        for k in range(n):
+            r = rng.random()
+            if r < 0.15:
+                out.append(b"")                                            # empty name
+            elif r < 0.3:
+                out.append(bytes(rng.randrange(1, 40)))                    # nothing but zero bytes
+            elif r < 0.4:
+                out.append(b"\x00\x00\x00\x05abcde\x00\x00\x00\x03xyz")    # looks like two more elements
+            elif r < 0.45:
+                out.append(bytes(rng.getrandbits(8) for _ in range(rng.randrange(256, 700))))   # prefix > 255
+            else:
+                out.append(bytes(rng.choice(b"abcdefghij0123456789") for _ in range(rng.randrange(1, 30))))
+        return out
+
+    c = synth.Corpus()
+    parts, xm, xid = [synth.frame(synth.connect_response(rng))], {}, 0
+
+    def add(fr, op):
+        nonlocal xid
+        parts.append(fr)
+        xm[xid] = op
+        xid += 1
+
+    add(kids_frame(xid, names_plain(3000), 12), 12)
+    add(synth.frame(synth.resp_header(xid, 1, 0) + synth.stat_bytes(rng)), 3)              # EXISTS reply in between
+    add(kids_frame(xid, names_nasty(4000), 12), 12)
+    add(kids_frame(xid, names_nasty(2500), 8, stat=False), 8)                              # GET_CHILDREN: no Stat
+    big = [b"a" * 20] * 50 + [bytes(rng.choice(b"xyz") for _ in range(20000))] + [b"b" * 9] * 900   # one name > a tile
+    add(kids_frame(xid, big, 12), 12)
+    add(kids_frame(xid, names_plain(2000), 12, count=2001), 12)                            # count lies: BAD_DECODE
+    add(kids_frame(xid, names_plain(2000), 12, count=1990), 12)                            # fewer than present: Stat read early
+    add(kids_frame(xid, names_plain(1500), 12, count=-5), 12)                              # negative count: empty vector
+    for n in (697, 698, 699, 700, 701, 1396, 1397):                                        # ends around tile / sub-range edges
+        add(kids_frame(xid, [b"0123456789ab"] * n, 12), 12)
+    add(synth.frame(synth.resp_header(-2, 3, 0)), 11)
+    add(kids_frame(xid, names_nasty(3000), 12), 12)                                        # last frame of the session
+    c.add(b"".join(parts), xidmap=xm)
+    # the same shapes as the very last bytes of the batch, and in a session of their own without handshake
+    c.add(kids_frame(0, names_nasty(1200), 12), hs=0, xidmap={0: 12})
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+    assert (o.status == 1).sum() >= 1 and g.n_buf > 15000
