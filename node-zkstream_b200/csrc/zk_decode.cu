@@ -212,6 +212,9 @@ struct GuessCtx {
 	XidWin xw;
 };
 
+/* 0x80 in every zero byte of w */
+__device__ __forceinline__ uint32_t mark_zero(uint32_t w) { return ~(((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w | 0x7f7f7f7fu); }
+__device__ __forceinline__ uint32_t nib_of(uint32_t t) { return (((t >> 7) * 0x00204081u) >> 21) & 0xfu; }
 /* bit i = byte i of w is zero (exact: no false positives), i = 0 is the byte at the lowest address */
 __device__ __forceinline__ uint32_t nib_zero(uint32_t w)
 {
@@ -220,11 +223,16 @@ __device__ __forceinline__ uint32_t nib_zero(uint32_t w)
 }
 __device__ __forceinline__ uint32_t mask16_zero(const uint4 &v)
 {
-	return nib_zero(v.x) | (nib_zero(v.y) << 4) | (nib_zero(v.z) << 8) | (nib_zero(v.w) << 12);
+	/* payload bytes (paths, random data) mostly hold no zero at all: one test spares the extraction */
+	const uint32_t t0 = mark_zero(v.x), t1 = mark_zero(v.y), t2 = mark_zero(v.z), t3 = mark_zero(v.w);
+	if (!(t0 | t1 | t2 | t3)) return 0u;
+	return nib_of(t0) | (nib_of(t1) << 4) | (nib_of(t2) << 8) | (nib_of(t3) << 12);
 }
 __device__ __forceinline__ uint32_t mask16_ff(const uint4 &v)
 {
-	return nib_zero(~v.x) | (nib_zero(~v.y) << 4) | (nib_zero(~v.z) << 8) | (nib_zero(~v.w) << 12);
+	const uint32_t t0 = mark_zero(~v.x), t1 = mark_zero(~v.y), t2 = mark_zero(~v.z), t3 = mark_zero(~v.w);
+	if (!(t0 | t1 | t2 | t3)) return 0u;
+	return nib_of(t0) | (nib_of(t1) << 4) | (nib_of(t2) << 8) | (nib_of(t3) << 12);
 }
 __device__ __forceinline__ uint32_t mask16_le1(const uint4 &v)
 {
@@ -286,7 +294,10 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 	if (gs + 16 <= padend) v0 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs));
 	if (gs + 32 <= padend) v1 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + gs + 16));
 	uint32_t z0 = mask16_zero(v0), z1 = mask16_zero(v1);
-	uint32_t f0 = g.server ? 0u : mask16_ff(v0), f1 = g.server ? 0u : mask16_ff(v1);
+	uint32_t f0 = mask16_ff(v0), f1 = mask16_ff(v1);
+	/* replies: with a table whose xids stay below 2^24 the xid's first byte is 0x00, or 0xff for the
+	 * special ones; the first byte of a zxid is one of the two as well (a miss only costs a fix-up) */
+	const bool xid_small = g.server || !g.xw.on || (g.xw.base >= 0 && g.xw.base + g.xw.count <= (1 << 24));
 	uint64_t blk = gs;            /* next 16 bytes to scan */
 	uint64_t cand = 0, cbase = 0; /* positions of a 64-byte group that passed the masks and are not tested yet */
 	for (;;) {
@@ -300,31 +311,38 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
 				v2 = zero4;
 				if (blk + 48 <= padend) v2 = __ldg(reinterpret_cast<const uint4 *>(a.bytes + blk + 32));
 				const uint32_t z2 = mask16_zero(v2);
-				const uint32_t f2 = g.server ? 0u : mask16_ff(v2);
+				const uint32_t f2 = mask16_ff(v2);
 				if (blk < g.lim) {
 					const uint64_t Z = (uint64_t)z0 | ((uint64_t)z1 << 16) | ((uint64_t)z2 << 32);
-					uint32_t c = mask16_le1(v0);
+					const uint64_t F = (uint64_t)f0 | ((uint64_t)f1 << 16) | ((uint64_t)f2 << 32);
+					uint32_t c;
 					if (g.server) {
-						c &= (uint32_t)(Z >> 8) & (uint32_t)(Z >> 9) & (uint32_t)(Z >> 10);
+						/* opcode 0..255 eight bytes in; xid small or special */
+						c = (uint32_t)(Z >> 8) & (uint32_t)(Z >> 9) & (uint32_t)(Z >> 10) & (uint32_t)((Z | F) >> 4);
 					} else {
-						const uint64_t F = (uint64_t)f0 | ((uint64_t)f1 << 16) | ((uint64_t)f2 << 32);
 						const uint32_t e0 = (uint32_t)(Z >> 16) & (uint32_t)(Z >> 17) & (uint32_t)(Z >> 18) & (uint32_t)(Z >> 19);
 						const uint32_t en = (uint32_t)(F >> 16) & (uint32_t)(F >> 17) & (uint32_t)(F >> 18);
-						c &= (e0 | en);
+						c = (e0 | en) & (uint32_t)((Z | F) >> 8);
+						if (xid_small) c &= (uint32_t)((Z | F) >> 4);
 					}
-					cand |= (uint64_t)(c & 0xffffu) << (16 * q);
+					c &= 0xffffu;
+					if (c) c &= mask16_le1(v0);      /* the length's first byte: only looked at where the rest fits */
+					cand |= (uint64_t)c << (16 * q);
 				}
 				v0 = v1; v1 = v2; z0 = z1; z1 = z2; f0 = f1; f1 = f2;
 			}
 		}
 		if (!cand) break;
-		const int k = __ffsll((long long)cand) - 1;
-		cand &= cand - 1;
-		const uint64_t p = cbase + (uint64_t)k;
-		if (!guess_local(g, p)) continue;
-		const int32_t len = (int32_t)g_be32(a.bytes, p);
-		if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS, g.xw))
-			return p;
+		/* every candidate of the group, in stream order */
+		while (cand) {
+			const int k = __ffsll((long long)cand) - 1;
+			cand &= cand - 1;
+			const uint64_t p = cbase + (uint64_t)k;
+			if (!guess_local(g, p)) continue;
+			const int32_t len = (int32_t)g_be32(a.bytes, p);
+			if (chain_plausible(a.bytes, p + 4 + (uint64_t)len, send, g.server, g.server ? ZK_GUESS_HOPS_SERVER : ZK_GUESS_HOPS, g.xw))
+				return p;
+		}
 	}
 	return ZK_NONE;
 }

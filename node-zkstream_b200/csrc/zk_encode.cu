@@ -139,7 +139,6 @@ __global__ void __launch_bounds__(ESC_THREADS) k_esc_apply(const uint32_t *sizes
 /* ---- span writer ----------------------------------------------------------------- */
 #define ENC_SPAN        4096u     /* output bytes per warp */
 #define ENC_WARPS       4
-#define ENC_INLINE_MAX  48        /* buffers up to this long are copied by the packet's own lane */
 
 __global__ void k_enc_spans(EncArgs a, uint32_t *span_first)
 {
@@ -149,24 +148,45 @@ __global__ void k_enc_spans(EncArgs a, uint32_t *span_first)
 	for (uint64_t s = (start + ENC_SPAN - 1) / ENC_SPAN; s * ENC_SPAN < end; ++s) span_first[s] = (uint32_t)i;
 }
 
-/* One lane's view of the span window: bytes of its packet that fall outside [s0, s1) are
- * dropped (another span's warp writes them). */
+/* ---- the span writer ------------------------------------------------------------------------
+ * One warp per 4 KiB span of the output.  Lane l takes packet (first + l) of the span and
+ *   1. writes the packet's integers (length prefix, xid, opcode, field lengths, flags ...) into the
+ *      span's shared-memory window, four byte stores each, in a fixed order of stages - header,
+ *      path, data, ACL, tail - so that lanes with different opcodes run the same code together;
+ *   2. files every buffer / string it has to copy as a job { arena offset, window range };
+ * then the warp splits into four groups of eight lanes that take jobs off the list until it is
+ * empty (aligned words built from two aligned source words, bytes at the ragged ends), and the
+ * window goes to HBM with 16-byte coalesced stores.  A packet that straddles spans is composed by
+ * each of them, clipped to its own bytes.  ConnectRequest / ConnectResponse / SET_WATCHES packets
+ * and ACL entries beyond the third take a plain per-lane path (LaneOut::put_buf_inline). */
+#define ENC_JOBS 192u
+
+struct EncJob { uint64_t src; uint32_t dlo, dhi; };     /* arena offset of the byte that lands at window offset dlo */
+
+struct __align__(16) EncSm {
+	uint8_t  win[ENC_SPAN];
+	EncJob   job[ENC_JOBS];
+	uint32_t njobs, next;
+};
+
+/* One lane's view of the span window: bytes of its packet that fall outside the span are dropped
+ * (another span's warp writes them).  Positions are relative to the span's first byte. */
 struct LaneOut {
-	uint8_t *win;
-	uint64_t s0, s1;
-	uint64_t pos;
+	EncSm   *sm;
+	int64_t  rel;        /* where the next byte goes, relative to the window (may be negative) */
+	int64_t  L;          /* bytes of the window in use */
 	__device__ __forceinline__ void put_byte(uint32_t v)      /* writeByte / writeBool jute-buffer.js:111-121 */
 	{
-		if (pos >= s0 && pos < s1) win[pos - s0] = (uint8_t)v;
-		pos += 1;
+		if (rel >= 0 && rel < L) sm->win[rel] = (uint8_t)v;
+		rel += 1;
 	}
 	__device__ __forceinline__ void put_int(int32_t v)        /* writeInt :141-147 */
 	{
-		if (pos >= s0 && pos + 4 <= s1) {
-			uint8_t *q = win + (pos - s0);
+		if (rel >= 0 && rel + 4 <= L) {
+			uint8_t *q = sm->win + rel;
 			q[0] = (uint8_t)((uint32_t)v >> 24); q[1] = (uint8_t)((uint32_t)v >> 16);
 			q[2] = (uint8_t)((uint32_t)v >> 8); q[3] = (uint8_t)v;
-			pos += 4;
+			rel += 4;
 		} else {
 #pragma unroll
 			for (int k = 0; k < 4; ++k) put_byte((uint32_t)v >> (24 - 8 * k));
@@ -177,42 +197,76 @@ struct LaneOut {
 		put_int((int32_t)((uint64_t)v >> 32));
 		put_int((int32_t)(uint64_t)v);
 	}
-	/* the part [k0, k1) of a len-byte field at `pos` that lies inside the span */
-	__device__ __forceinline__ void clip(uint32_t len, uint32_t &k0, uint32_t &k1) const
+	/* the bytes of a buffer, copied by this lane */
+	__device__ __forceinline__ void copy_inline(const uint8_t *arena, uint64_t off, uint32_t len)
 	{
-		k0 = pos < s0 ? (uint32_t)((s0 - pos) < (uint64_t)len ? (s0 - pos) : (uint64_t)len) : 0u;
-		k1 = pos + len <= s1 ? len : (pos < s1 ? (uint32_t)(s1 - pos) : 0u);
-		if (k1 < k0) k1 = k0;
+		int64_t k0 = rel < 0 ? -rel : 0, k1 = rel + (int64_t)len <= L ? (int64_t)len : L - rel;
+		if (k0 > (int64_t)len) k0 = len;
+		for (int64_t k = k0; k < k1; ++k) sm->win[rel + k] = __ldg(arena + off + (uint64_t)k);
+		rel += len;
 	}
-	/* writeBuffer (:123-134): length (-1 when empty), then the bytes — here, or as a job */
-	__device__ __forceinline__ void put_buf(const uint8_t *arena, uint64_t off, int32_t len, bool may_defer,
-	    uint64_t &job_src, uint32_t &job_len, uint64_t &job_dst)
+	/* writeBuffer (:123-134): length (-1 when empty), then the bytes, as a job for the warp */
+	__device__ __forceinline__ void put_buf(const uint8_t *arena, uint64_t off, int32_t len)
 	{
 		if (len <= 0) { put_int(-1); return; }
 		put_int(len);
-		if (may_defer && len > ENC_INLINE_MAX) {
-			job_src = off; job_len = (uint32_t)len; job_dst = pos;
-		} else {
-			uint32_t k0, k1;
-			clip((uint32_t)len, k0, k1);
-			const uint8_t *src = arena + off;
-			uint8_t *dst = win + (pos + k0 - s0);
-			for (uint32_t k = k0; k < k1; ++k) *dst++ = __ldg(src + k);
+		const int64_t lo = rel < 0 ? 0 : rel, hi = rel + len < L ? rel + len : L;
+		if (hi > lo) {
+			const uint32_t j = atomicAdd(&sm->njobs, 1u);
+			if (j < ENC_JOBS) {
+				EncJob e;
+				e.src = off + (uint64_t)(lo - rel); e.dlo = (uint32_t)lo; e.dhi = (uint32_t)hi;
+				sm->job[j] = e;
+				rel += len;
+				return;
+			}
+			copy_inline(arena, off, (uint32_t)len);      /* list full: this lane copies */
+			return;
 		}
-		pos += (uint32_t)len;
+		rel += len;
+	}
+	__device__ __forceinline__ void put_buf_inline(const uint8_t *arena, uint64_t off, int32_t len)
+	{
+		if (len <= 0) { put_int(-1); return; }
+		put_int(len);
+		copy_inline(arena, off, (uint32_t)len);
 	}
 };
+
+/* eight lanes copy one job: bytes [e.dlo, e.dhi) of the window from the arena */
+__device__ __forceinline__ void enc_copy_job(EncSm &sm, const uint8_t *arena, uint64_t arena_len, const EncJob e, const uint32_t gl)
+{
+	const uint32_t n = e.dhi - e.dlo;
+	uint8_t *dp = sm.win + e.dlo;
+	const uint8_t *sp = arena + e.src;
+	if (n < 24 || e.src + n + 8 > arena_len) {
+		for (uint32_t k = gl; k < n; k += 8) dp[k] = __ldg(sp + k);
+		return;
+	}
+	const uint32_t head = (4u - (e.dlo & 3u)) & 3u;
+	if (gl < head) dp[gl] = __ldg(sp + gl);
+	const uint32_t nw = (n - head) >> 2;
+	const uint32_t mis = (uint32_t)((uintptr_t)(sp + head) & 3u);
+	const uint32_t *sw = reinterpret_cast<const uint32_t *>(sp + head - mis);
+	uint32_t *dw = reinterpret_cast<uint32_t *>(dp + head);
+	if (mis) {
+		for (uint32_t q = gl; q < nw; q += 8) dw[q] = __funnelshift_r(__ldg(sw + q), __ldg(sw + q + 1), mis * 8);
+	} else {
+		for (uint32_t q = gl; q < nw; q += 8) dw[q] = __ldg(sw + q);
+	}
+	for (uint32_t k = head + 4 * nw + gl; k < n; k += 8) dp[k] = __ldg(sp + k);
+}
 
 __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const uint32_t *span_first, uint64_t out_len,
     int aligned16)
 {
-	__shared__ __align__(16) uint8_t s_win[ENC_WARPS][ENC_SPAN];
+	__shared__ EncSm s_all[ENC_WARPS];
 	const uint32_t lane = threadIdx.x & 31;
 	const uint64_t span = (uint64_t)blockIdx.x * ENC_WARPS + (threadIdx.x >> 5);
 	const uint64_t s0 = span * ENC_SPAN;
 	if (s0 >= out_len) return;
 	const uint64_t s1 = s0 + ENC_SPAN < out_len ? s0 + ENC_SPAN : out_len;
-	uint8_t *win = s_win[threadIdx.x >> 5];
+	EncSm &sm = s_all[threadIdx.x >> 5];
 	const zkb_requests &r = a.r;
 
 	for (uint64_t base = span_first[span];; base += 32) {
@@ -220,107 +274,96 @@ __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const u
 		const bool valid = i < r.n;
 		const uint64_t start = valid ? a.frame_off[i] : ~0ull;
 		if (!__any_sync(0xffffffffu, valid && start < s1)) break;
-		uint64_t j_src[2] = { 0, 0 }, j_dst[2] = { 0, 0 };
-		uint32_t j_len[2] = { 0, 0 };
+		if (lane == 0) { sm.njobs = 0; sm.next = 0; }
+		__syncwarp();
+		uint64_t end = 0;
+		bool live = false;
 		if (valid && start < s1 && a.status[i] == ZKB_ENC_OK) {
-			const uint64_t end = a.frame_off[i + 1];
-			if (end > s0 && end > start) {
-				LaneOut w;
-				w.win = win; w.s0 = s0; w.s1 = s1; w.pos = start;
-				const int op = r.op[i];
-				w.put_int((int32_t)(end - start - 4));             /* writeLengthPrefixed :181-189 */
-				/* what follows the header, by opcode (zk-buffer.js:97-136; connect: :32-39, :50-56) */
-				bool f_path = false, f_data = false, f_acl = false, f_byte = false, f_int = false, f_watch = false;
-				if (op == ZKB_ENC_CONNECT_REQUEST) {
-					w.put_int(r.a0[i]); w.put_long(r.zxid2[i]); w.put_int(r.a1[i]); w.put_long(r.zxid[i]);
-					f_data = true;
-				} else if (op == ZKB_ENC_CONNECT_RESPONSE) {
-					w.put_int(r.a0[i]); w.put_int(r.a1[i]); w.put_long(r.zxid[i]);
-					f_data = true;
+			end = a.frame_off[i + 1];
+			live = end > s0 && end > start;
+		}
+		int op = 0;
+		LaneOut w;
+		w.sm = &sm; w.L = (int64_t)(s1 - s0); w.rel = 0;
+		/* which stages the packet goes through (zk-buffer.js:97-136; connect: :32-39, :50-56) */
+		bool f_path = false, f_data = false, f_acl = false, f_byte = false, f_int = false, f_other = false;
+		if (live) {
+			op = r.op[i];
+			w.rel = (int64_t)start - (int64_t)s0;
+			w.put_int((int32_t)(end - start - 4));                 /* writeLengthPrefixed :181-189 */
+			switch (op) {
+			case ZKB_OP_GET_CHILDREN: case ZKB_OP_GET_CHILDREN2: case ZKB_OP_GET_DATA: case ZKB_OP_EXISTS:
+				f_path = true; f_byte = true; break;
+			case ZKB_OP_CREATE: f_path = true; f_data = true; f_acl = true; f_int = true; break;
+			case ZKB_OP_DELETE: f_path = true; f_int = true; break;
+			case ZKB_OP_GET_ACL: case ZKB_OP_SYNC: f_path = true; break;
+			case ZKB_OP_SET_DATA: f_path = true; f_data = true; f_int = true; break;
+			case ZKB_OP_CLOSE_SESSION: case ZKB_OP_PING: break;        /* header only (:129-132) */
+			default: f_other = true; break;                            /* connect packets, SET_WATCHES */
+			}
+		}
+		if (live && !f_other) { w.put_int(r.xid[i]); w.put_int(op); }
+		if (f_other) {
+			if (op == ZKB_ENC_CONNECT_REQUEST) {
+				w.put_int(r.a0[i]); w.put_long(r.zxid2[i]); w.put_int(r.a1[i]); w.put_long(r.zxid[i]);
+				w.put_buf_inline(r.arena, r.data_off[i], r.data_len[i]);
+			} else if (op == ZKB_ENC_CONNECT_RESPONSE) {
+				w.put_int(r.a0[i]); w.put_int(r.a1[i]); w.put_long(r.zxid[i]);
+				w.put_buf_inline(r.arena, r.data_off[i], r.data_len[i]);
+			} else {                                                   /* SET_WATCHES :255-273 */
+				const int32_t n0 = r.n0[i], n1 = r.n1[i], n2 = r.vec_count[i] - n0 - n1;
+				uint64_t e = r.vec_first[i];
+				w.put_int(r.xid[i]); w.put_int(op);
+				w.put_long(r.zxid[i]);
+				w.put_int(n0);
+				for (int32_t k = 0; k < n0; ++k, ++e) w.put_buf_inline(r.arena, r.elem_off[e], r.elem_len[e]);
+				w.put_int(n1);
+				for (int32_t k = 0; k < n1; ++k, ++e) w.put_buf_inline(r.arena, r.elem_off[e], r.elem_len[e]);
+				w.put_int(n2);
+				for (int32_t k = 0; k < n2; ++k, ++e) w.put_buf_inline(r.arena, r.elem_off[e], r.elem_len[e]);
+			}
+		}
+		if (f_path) w.put_buf(r.arena, r.path_off[i], r.path_len[i]);
+		if (f_data) w.put_buf(r.arena, r.data_off[i], r.data_len[i]);
+		if (f_acl) {                                                   /* writeACL :384-393 */
+			const int32_t cnt = r.vec_count[i];
+			w.put_int(cnt);
+			for (int32_t k = 0; k < cnt; ++k) {
+				const uint64_t q = (uint64_t)r.vec_first[i] + (uint64_t)k;
+				w.put_int(r.acl_perms[q]);
+				if (k < 3) {
+					w.put_buf(r.arena, r.acl_scheme_off[q], r.acl_scheme_len[q]);
+					w.put_buf(r.arena, r.acl_id_off[q], r.acl_id_len[q]);
 				} else {
-					w.put_int(r.xid[i]);
-					w.put_int(op);
-					switch (op) {
-					case ZKB_OP_GET_CHILDREN: case ZKB_OP_GET_CHILDREN2: case ZKB_OP_GET_DATA: case ZKB_OP_EXISTS:
-						f_path = true; f_byte = true; break;
-					case ZKB_OP_CREATE: f_path = true; f_data = true; f_acl = true; f_int = true; break;
-					case ZKB_OP_DELETE: f_path = true; f_int = true; break;
-					case ZKB_OP_GET_ACL: case ZKB_OP_SYNC: f_path = true; break;
-					case ZKB_OP_SET_DATA: f_path = true; f_data = true; f_int = true; break;
-					case ZKB_OP_SET_WATCHES: f_watch = true; break;
-					default: break;   /* CLOSE_SESSION, PING: header only (:129-132) */
-					}
+					w.put_buf_inline(r.arena, r.acl_scheme_off[q], r.acl_scheme_len[q]);
+					w.put_buf_inline(r.arena, r.acl_id_off[q], r.acl_id_len[q]);
 				}
-				if (f_watch) {                                      /* :255-273 */
-					const int32_t n0 = r.n0[i], n1 = r.n1[i], n2 = r.vec_count[i] - n0 - n1;
-					uint64_t e = r.vec_first[i];
-					uint64_t x0; uint32_t x1; uint64_t x2;
-					w.put_long(r.zxid[i]);
-					w.put_int(n0);
-					for (int32_t k = 0; k < n0; ++k, ++e) w.put_buf(r.arena, r.elem_off[e], r.elem_len[e], false, x0, x1, x2);
-					w.put_int(n1);
-					for (int32_t k = 0; k < n1; ++k, ++e) w.put_buf(r.arena, r.elem_off[e], r.elem_len[e], false, x0, x1, x2);
-					w.put_int(n2);
-					for (int32_t k = 0; k < n2; ++k, ++e) w.put_buf(r.arena, r.elem_off[e], r.elem_len[e], false, x0, x1, x2);
-				}
-				if (f_path) w.put_buf(r.arena, r.path_off[i], r.path_len[i], true, j_src[0], j_len[0], j_dst[0]);
-				if (f_data) w.put_buf(r.arena, r.data_off[i], r.data_len[i], true, j_src[1], j_len[1], j_dst[1]);
-				if (f_acl) {                                        /* writeACL :384-393 */
-					const int32_t cnt = r.vec_count[i];
-					uint64_t x0; uint32_t x1; uint64_t x2;
-					w.put_int(cnt);
-					for (int32_t k = 0; k < cnt; ++k) {
-						const uint64_t q = (uint64_t)r.vec_first[i] + (uint64_t)k;
-						w.put_int(r.acl_perms[q]);
-						w.put_buf(r.arena, r.acl_scheme_off[q], r.acl_scheme_len[q], false, x0, x1, x2);
-						w.put_buf(r.arena, r.acl_id_off[q], r.acl_id_len[q], false, x0, x1, x2);
-					}
-				}
-				if (f_byte) w.put_byte(r.a0[i] ? 1 : 0);
-				if (f_int) w.put_int(r.a0[i]);
 			}
 		}
-		/* the long buffers of these 32 packets, copied by the whole warp, 4 bytes per lane */
-#pragma unroll
-		for (int slot = 0; slot < 2; ++slot) {
-			uint32_t m = __ballot_sync(0xffffffffu, j_len[slot] != 0);
-			while (m) {
-				const int src_lane = __ffs(m) - 1;
-				m &= m - 1;
-				const uint64_t src = __shfl_sync(0xffffffffu, j_src[slot], src_lane);
-				const uint64_t dst = __shfl_sync(0xffffffffu, j_dst[slot], src_lane);
-				const uint32_t len = __shfl_sync(0xffffffffu, j_len[slot], src_lane);
-				const uint64_t lo = dst > s0 ? dst : s0;
-				const uint64_t hi = dst + len < s1 ? dst + len : s1;
-				if (hi <= lo) continue;
-				const uint64_t so = src + (lo - dst);            /* first source byte, arena-relative */
-				const uint8_t *sp = r.arena + so;
-				uint8_t *dp = win + (lo - s0);
-				const uint32_t cnt = (uint32_t)(hi - lo);
-				/* head bytes up to a 4-byte aligned window address, aligned words built from two
-				 * aligned source words, tail bytes; the last source word is only read whole when
-				 * it lies inside the arena */
-				uint32_t head = (4u - ((uint32_t)(lo - s0) & 3u)) & 3u;
-				if (head > cnt) head = cnt;
-				if (lane < head) dp[lane] = __ldg(sp + lane);
-				uint32_t nw = (cnt - head) >> 2;
-				while (nw && so + head + 4ull * nw + 3 >= r.arena_len) --nw;
-				const uint32_t mis = (uint32_t)((uintptr_t)(sp + head) & 3u);
-				const uint32_t *sw = reinterpret_cast<const uint32_t *>(sp + head - mis);
-				uint32_t *dw = reinterpret_cast<uint32_t *>(dp + head);
-				for (uint32_t q = lane; q < nw; q += 32) {
-					const uint32_t x = __ldg(sw + q);
-					dw[q] = mis ? __funnelshift_r(x, __ldg(sw + q + 1), mis * 8) : x;
-				}
-				for (uint32_t k = head + 4 * nw + lane; k < cnt; k += 32) dp[k] = __ldg(sp + k);
+		if (f_byte) w.put_byte(r.a0[i] ? 1 : 0);
+		if (f_int) w.put_int(r.a0[i]);
+		__syncwarp();
+		/* the copies of these 32 packets: four groups of eight lanes take jobs until none is left */
+		{
+			const uint32_t nj = sm.njobs < ENC_JOBS ? sm.njobs : ENC_JOBS;
+			const uint32_t gl = lane & 7u;
+			const uint32_t gmask = 0xffu << (lane & 24u);      /* the groups leave the loop at different times */
+			for (;;) {
+				uint32_t j = 0;
+				if (gl == 0) j = atomicAdd(&sm.next, 1u);
+				j = __shfl_sync(gmask, j, lane & 24u);
+				if (j >= nj) break;
+				enc_copy_job(sm, r.arena, r.arena_len, sm.job[j], gl);
 			}
 		}
+		__syncwarp();
 		if (!__any_sync(0xffffffffu, valid && start < s1 && lane == 31)) break;   /* the last lane was past the span */
 	}
 	__syncwarp();
 	/* window -> HBM */
 	const uint32_t L = (uint32_t)(s1 - s0);
 	uint8_t *dst = a.out + s0;
+	const uint8_t *win = sm.win;
 	if (aligned16) {
 		const uint32_t full = L & ~15u;
 		for (uint32_t k = lane * 16; k < full; k += 512)

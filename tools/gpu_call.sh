@@ -9,7 +9,4 @@ B="--steps 5 --warmup 3 --no-cpu --no-encode"
 for c in cfg2 cfg4 cfg3 cfg1; do
   timeout 600 python bench.py --config $c $B > $O/b_$c.json 2> $O/b_$c.err; echo "$c rc=$?"; python tools/bench_brief.py $O/b_$c.json; tail -2 $O/b_$c.err
 done
-python tools/profile_all.py 1 1 > $O/profall_plain.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_split" -c 2 -o $O/r2_ksplit -f python tools/profile_all.py 1 1 > $O/ncu_ksplit.log 2>&1; echo "ncu rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_decode" -c 2 -o $O/r2_kdec -f python tools/profile_all.py 1 1 > $O/ncu_kdec.log 2>&1; echo "ncu2 rc=$?"
 du -sm $O
