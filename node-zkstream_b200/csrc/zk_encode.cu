@@ -159,14 +159,15 @@ __global__ void k_enc_spans(EncArgs a, uint32_t *span_first)
  * window goes to HBM with 16-byte coalesced stores.  A packet that straddles spans is composed by
  * each of them, clipped to its own bytes.  ConnectRequest / ConnectResponse / SET_WATCHES packets
  * and ACL entries beyond the third take a plain per-lane path (LaneOut::put_buf_inline). */
-#define ENC_JOBS 192u
+#define ENC_JOBS 88u
 
 struct EncJob { uint64_t src; uint32_t dlo, dhi; };     /* arena offset of the byte that lands at window offset dlo */
 
+#define ENC_SHORT 64u      /* jobs up to this many bytes are copied by one lane each, longer ones by eight lanes */
 struct __align__(16) EncSm {
 	uint8_t  win[ENC_SPAN];
-	EncJob   job[ENC_JOBS];
-	uint32_t njobs, next;
+	EncJob   job[ENC_JOBS];  /* short jobs from the bottom, long jobs from the top */
+	uint32_t nshort, nlong, next;
 };
 
 /* One lane's view of the span window: bytes of its packet that fall outside the span are dropped
@@ -212,11 +213,13 @@ struct LaneOut {
 		put_int(len);
 		const int64_t lo = rel < 0 ? 0 : rel, hi = rel + len < L ? rel + len : L;
 		if (hi > lo) {
-			const uint32_t j = atomicAdd(&sm->njobs, 1u);
-			if (j < ENC_JOBS) {
+			const bool small = (uint32_t)(hi - lo) <= ENC_SHORT;
+			const uint32_t j = atomicAdd(small ? &sm->nshort : &sm->nlong, 1u);
+			/* the two ends may not meet: either counter alone stays below half the list */
+			if (j < ENC_JOBS / 2) {
 				EncJob e;
 				e.src = off + (uint64_t)(lo - rel); e.dlo = (uint32_t)lo; e.dhi = (uint32_t)hi;
-				sm->job[j] = e;
+				sm->job[small ? j : ENC_JOBS - 1 - j] = e;
 				rel += len;
 				return;
 			}
@@ -232,6 +235,33 @@ struct LaneOut {
 		copy_inline(arena, off, (uint32_t)len);
 	}
 };
+
+/* one lane copies one short job: every lane of the warp has its own job in flight, so the arena
+ * reads of 32 strings overlap instead of queueing behind each other */
+__device__ __forceinline__ void enc_copy_short(EncSm &sm, const uint8_t *arena, uint64_t arena_len, const EncJob e)
+{
+	const uint32_t n = e.dhi - e.dlo;
+	uint8_t *dp = sm.win + e.dlo;
+	const uint8_t *sp = arena + e.src;
+	if (n < 8 || e.src + n + 8 > arena_len) {
+		for (uint32_t k = 0; k < n; ++k) dp[k] = __ldg(sp + k);
+		return;
+	}
+	const uint32_t head = (4u - (e.dlo & 3u)) & 3u;
+	for (uint32_t k = 0; k < head; ++k) dp[k] = __ldg(sp + k);
+	const uint32_t nw = (n - head) >> 2;
+	const uint32_t mis = (uint32_t)((uintptr_t)(sp + head) & 3u);
+	const uint32_t *sw = reinterpret_cast<const uint32_t *>(sp + head - mis);
+	uint32_t *dw = reinterpret_cast<uint32_t *>(dp + head);
+	uint32_t x0 = __ldg(sw);
+#pragma unroll 4
+	for (uint32_t q = 0; q < nw; ++q) {
+		const uint32_t x1 = mis ? __ldg(sw + q + 1) : 0u;
+		dw[q] = mis ? __funnelshift_r(x0, x1, mis * 8) : x0;
+		x0 = mis ? x1 : __ldg(sw + q + 1);
+	}
+	for (uint32_t k = head + 4 * nw; k < n; ++k) dp[k] = __ldg(sp + k);
+}
 
 /* eight lanes copy one job: bytes [e.dlo, e.dhi) of the window from the arena */
 __device__ __forceinline__ void enc_copy_job(EncSm &sm, const uint8_t *arena, uint64_t arena_len, const EncJob e, const uint32_t gl)
@@ -257,7 +287,7 @@ __device__ __forceinline__ void enc_copy_job(EncSm &sm, const uint8_t *arena, ui
 	for (uint32_t k = head + 4 * nw + gl; k < n; k += 8) dp[k] = __ldg(sp + k);
 }
 
-__global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const uint32_t *span_first, uint64_t out_len,
+__global__ void __launch_bounds__(ENC_WARPS * 32, 10) k_enc_write(EncArgs a, const uint32_t *span_first, uint64_t out_len,
     int aligned16)
 {
 	__shared__ EncSm s_all[ENC_WARPS];
@@ -274,7 +304,7 @@ __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const u
 		const bool valid = i < r.n;
 		const uint64_t start = valid ? a.frame_off[i] : ~0ull;
 		if (!__any_sync(0xffffffffu, valid && start < s1)) break;
-		if (lane == 0) { sm.njobs = 0; sm.next = 0; }
+		if (lane == 0) { sm.nshort = 0; sm.nlong = 0; sm.next = 0; }
 		__syncwarp();
 		uint64_t end = 0;
 		bool live = false;
@@ -287,8 +317,17 @@ __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const u
 		w.sm = &sm; w.L = (int64_t)(s1 - s0); w.rel = 0;
 		/* which stages the packet goes through (zk-buffer.js:97-136; connect: :32-39, :50-56) */
 		bool f_path = false, f_data = false, f_acl = false, f_byte = false, f_int = false, f_other = false;
+		/* the packet's scalar columns, fetched together (one round trip instead of one per stage);
+		 * a column the caller left out reads as zero, as before */
+		int32_t c_xid = 0, c_a0 = 0, c_plen = 0, c_dlen = 0, c_vcnt = 0;
+		uint64_t c_poff = 0, c_doff = 0, c_vfirst = 0;
 		if (live) {
 			op = r.op[i];
+			if (r.xid) c_xid = r.xid[i];
+			if (r.a0) c_a0 = r.a0[i];
+			if (r.path_len) { c_plen = r.path_len[i]; c_poff = r.path_off[i]; }
+			if (r.data_len) { c_dlen = r.data_len[i]; c_doff = r.data_off[i]; }
+			if (r.vec_count) { c_vcnt = r.vec_count[i]; c_vfirst = r.vec_first[i]; }
 			w.rel = (int64_t)start - (int64_t)s0;
 			w.put_int((int32_t)(end - start - 4));                 /* writeLengthPrefixed :181-189 */
 			switch (op) {
@@ -302,7 +341,7 @@ __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const u
 			default: f_other = true; break;                            /* connect packets, SET_WATCHES */
 			}
 		}
-		if (live && !f_other) { w.put_int(r.xid[i]); w.put_int(op); }
+		if (live && !f_other) { w.put_int(c_xid); w.put_int(op); }
 		if (f_other) {
 			if (op == ZKB_ENC_CONNECT_REQUEST) {
 				w.put_int(r.a0[i]); w.put_long(r.zxid2[i]); w.put_int(r.a1[i]); w.put_long(r.zxid[i]);
@@ -323,13 +362,13 @@ __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const u
 				for (int32_t k = 0; k < n2; ++k, ++e) w.put_buf_inline(r.arena, r.elem_off[e], r.elem_len[e]);
 			}
 		}
-		if (f_path) w.put_buf(r.arena, r.path_off[i], r.path_len[i]);
-		if (f_data) w.put_buf(r.arena, r.data_off[i], r.data_len[i]);
+		if (f_path) w.put_buf(r.arena, c_poff, c_plen);
+		if (f_data) w.put_buf(r.arena, c_doff, c_dlen);
 		if (f_acl) {                                                   /* writeACL :384-393 */
-			const int32_t cnt = r.vec_count[i];
+			const int32_t cnt = c_vcnt;
 			w.put_int(cnt);
 			for (int32_t k = 0; k < cnt; ++k) {
-				const uint64_t q = (uint64_t)r.vec_first[i] + (uint64_t)k;
+				const uint64_t q = c_vfirst + (uint64_t)k;
 				w.put_int(r.acl_perms[q]);
 				if (k < 3) {
 					w.put_buf(r.arena, r.acl_scheme_off[q], r.acl_scheme_len[q]);
@@ -340,20 +379,23 @@ __global__ void __launch_bounds__(ENC_WARPS * 32) k_enc_write(EncArgs a, const u
 				}
 			}
 		}
-		if (f_byte) w.put_byte(r.a0[i] ? 1 : 0);
-		if (f_int) w.put_int(r.a0[i]);
+		if (f_byte) w.put_byte(c_a0 ? 1 : 0);
+		if (f_int) w.put_int(c_a0);
 		__syncwarp();
-		/* the copies of these 32 packets: four groups of eight lanes take jobs until none is left */
+		/* the copies of these 32 packets: short ones one per lane, long ones taken by four groups of
+		 * eight lanes until none is left */
 		{
-			const uint32_t nj = sm.njobs < ENC_JOBS ? sm.njobs : ENC_JOBS;
+			const uint32_t ns = sm.nshort < ENC_JOBS / 2 ? sm.nshort : ENC_JOBS / 2;
+			const uint32_t nl = sm.nlong < ENC_JOBS / 2 ? sm.nlong : ENC_JOBS / 2;
+			for (uint32_t j = lane; j < ns; j += 32) enc_copy_short(sm, r.arena, r.arena_len, sm.job[j]);
 			const uint32_t gl = lane & 7u;
 			const uint32_t gmask = 0xffu << (lane & 24u);      /* the groups leave the loop at different times */
 			for (;;) {
 				uint32_t j = 0;
 				if (gl == 0) j = atomicAdd(&sm.next, 1u);
 				j = __shfl_sync(gmask, j, lane & 24u);
-				if (j >= nj) break;
-				enc_copy_job(sm, r.arena, r.arena_len, sm.job[j], gl);
+				if (j >= nl) break;
+				enc_copy_job(sm, r.arena, r.arena_len, sm.job[ENC_JOBS - 1 - j], gl);
 			}
 		}
 		__syncwarp();
