@@ -279,16 +279,18 @@ void zkb_ctx_destroy(zkb_ctx *ctx);
 const char *zkb_last_error(const zkb_ctx *ctx);
 /* Number of CUDA kernels this context has launched so far (for bench accounting). */
 uint64_t zkb_kernel_launches(const zkb_ctx *ctx);
-/* Number of extra splitter iterations (entry-point guesses that had to be corrected) this
- * context has needed so far; 0 on ordinary traffic.  Diagnostic only. */
+/* Number of splitter fix-up rounds (entry-point guesses that had to be corrected) this context
+ * has needed so far; one per batch is normal, more on payloads that look like frames.  Diagnostic only. */
 uint64_t zkb_split_fixups(const zkb_ctx *ctx);
 /* Decode passes this context has had to run twice.  The splitter predicts from the frame
  * headers how many side-table rows every chunk will produce, so that the decode kernel can
  * place rows without waiting for the chunks before it; a frame that does not keep what its
  * header promises (malformed body, handshake deeper than the splitter can see) is noticed by
- * the kernel, and the batch is decoded again from that frame's chunk onwards with ordered
- * look-back placement — same result, at most one extra decode kernel.  0 on well-formed traffic.  ZKBATCH_NO_PREDICT=1 in the environment
- * (read at zkb_ctx_create) turns the prediction off.  Diagnostic only. */
+ * the kernel, and the batch is decoded again from that frame's chunk onwards by the exact
+ * route (count the rows of every chunk, one scan, place) — same result, at most one more pass over
+ * the rest of the batch, and no chunk ever waits for another.  0 on well-formed traffic.
+ * ZKBATCH_NO_PREDICT=1 in the environment (read at zkb_ctx_create) turns the prediction off: every
+ * batch then takes the exact route.  Diagnostic only. */
 uint64_t zkb_row_mispredicts(const zkb_ctx *ctx);
 /* Frames of the last decode call that were not well-formed (or reached past the staged
  * tile) and therefore went through the exact, slower reader.  Diagnostic only. */
