@@ -220,6 +220,10 @@ typedef struct zkb_decoded {
 	uint64_t *sess_consumed;      /* [nsessions] batch-absolute end of the last complete frame */
 	uint64_t *sess_bad_length_at; /* [nsessions] */
 	uint32_t *sess_first_frame;   /* [nsessions + 1] */
+
+	/* compact replay results only (zkb_ctx_set_replay_compact), NULL otherwise: per BUF row the
+	 * offset of the buffer's first byte from the length prefix of the frame that owns it */
+	uint32_t *buf_rel;
 } zkb_decoded;
 
 /* ---- encode input (struct of arrays) ----------------------------------------------
@@ -350,6 +354,23 @@ int zkb_decode_host(zkb_ctx *ctx, const uint8_t *bytes, uint64_t nbytes,
  */
 typedef int (*zkb_slice_cb)(void *user, uint32_t first_session, uint32_t nsessions,
     const zkb_decoded *req, const zkb_decoded *rsp);
+
+/*
+ * Compact replay results.  With several GPUs on one host the download of the result columns,
+ * not the upload of the capture, is what the host's PCIe complex runs out of first
+ * (profiles/pcie_peak_n*.json), and more than a third of those bytes can be worked out from the
+ * rest.  With compact mode on, zkb_replay_host leaves these columns out (their pointers are NULL
+ * in the structs handed to the callback):
+ *   frame_off    frames of a session lie back to back from the session's first byte:
+ *                frame_off[f] = off[s] + sum over the session's earlier frames of (4 + frame_len)
+ *   session      from sess_first_frame
+ *   stat_frame, buf_frame, acl_frame   the rows of a frame follow those of the frame before it, and how
+ *                many rows a frame owns follows from meta / err / a0 / a1 (see the column list above)
+ *   buf_off      replaced by buf_rel (32 bits): buf_off = frame_off[owner] + buf_rel
+ * Everything else is delivered as usual.  node-zkstream_b200/columns.py (Columns.restore_derived)
+ * is the reference implementation of putting the columns back.  Off by default.
+ */
+int zkb_ctx_set_replay_compact(zkb_ctx *ctx, int on);
 
 int zkb_replay_host(zkb_ctx *ctx,
     const uint8_t *req_bytes, uint64_t req_nbytes, const zkb_sessions *req_sess,

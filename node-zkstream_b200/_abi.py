@@ -46,7 +46,8 @@ SESS_COLS = [("sess_consumed", "u8"), ("sess_bad_length_at", "u8"), ("sess_first
 class Decoded(C.Structure):
     _fields_ = ([(n, C.c_uint64) for n in ("cap_frames", "cap_stat", "cap_buf", "cap_acl",
                                             "n_frames", "n_stat", "n_buf", "n_acl")] +
-                [(n, P) for n, _ in FRAME_COLS + STAT_COLS + BUF_COLS + ACL_COLS + SESS_COLS])
+                [(n, P) for n, _ in FRAME_COLS + STAT_COLS + BUF_COLS + ACL_COLS + SESS_COLS] +
+                [("buf_rel", P)])      # compact replay results only
 
 
 REQ_COLS = [("xid", "i4"), ("op", "i1"), ("path_off", "u8"), ("path_len", "i4"), ("data_off", "u8"),
@@ -84,6 +85,7 @@ SYMBOLS = [
     ("zkb_last_slow_frames", C.c_uint64, [P]),
     ("zkb_ctx_set_timing", C.c_int, [P, C.c_int]),
     ("zkb_last_phase_ms", C.c_int, [P, C.POINTER(C.c_float * 3)]),
+    ("zkb_ctx_set_replay_compact", C.c_int, [P, C.c_int]),
     ("zkb_ctx_stream", P, [P]),
     ("zkb_ctx_sync", C.c_int, [P]),
     ("zkb_decode_scratch_bytes", C.c_uint64, [C.c_uint64, C.c_uint32]),

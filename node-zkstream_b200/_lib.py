@@ -143,6 +143,11 @@ class Context:
     def set_timing(self, on=True):
         self._check(self._lib.zkb_ctx_set_timing(self._h, 1 if on else 0))
 
+    def set_replay_compact(self, on=True):
+        """zkb_replay_host leaves the derivable columns out of the download (Columns.restore_derived
+        puts them back): see zkb_ctx_set_replay_compact."""
+        self._check(self._lib.zkb_ctx_set_replay_compact(self._h, 1 if on else 0))
+
     def last_phase_ms(self):
         """(split, emit, decode) device milliseconds of the last decode call (timing must be on)."""
         out = (C.c_float * 3)()

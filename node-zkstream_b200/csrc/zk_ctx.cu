@@ -127,6 +127,12 @@ ZKB_EXPORT int zkb_ctx_set_timing(zkb_ctx *ctx, int on)
 	ctx->timing = on ? 1 : 0;
 	return ZKB_OK;
 }
+ZKB_EXPORT int zkb_ctx_set_replay_compact(zkb_ctx *ctx, int on)
+{
+	if (!ctx) return ZKB_EINVAL;
+	ctx->replay_compact = on ? 1 : 0;
+	return ZKB_OK;
+}
 ZKB_EXPORT int zkb_last_phase_ms(const zkb_ctx *ctx, float out[3])
 {
 	if (!ctx || !out) return ZKB_EINVAL;
@@ -207,6 +213,59 @@ static int copy_decoded_d2h(zkb_ctx *ctx, const zkb_decoded *dv, zkb_decoded *hv
 	CP(buf_frame, nb); CP(buf_off, nb); CP(buf_len, nb);
 	CP(acl_frame, na); CP(acl_perms, na);
 	CP(sess_consumed, nsess); CP(sess_bad_length_at, nsess); CP(sess_first_frame, (uint64_t)nsess + 1);
+#undef CP
+	hv->n_frames = nf; hv->n_stat = ns; hv->n_buf = nb; hv->n_acl = na;
+	return ZKB_OK;
+}
+
+/* compact replay results: the columns that cannot be derived, buf_rel in place of buf_off */
+static size_t carve_compact(zkb_decoded *d, uint8_t *base, uint64_t cf, uint64_t cs, uint64_t cb,
+    uint64_t ca, uint32_t nsess)
+{
+	Carver c = { base, 0 };
+	memset(d, 0, sizeof (*d));
+	d->cap_frames = cf; d->cap_stat = cs; d->cap_buf = cb; d->cap_acl = ca;
+	d->frame_len = c.take<int32_t>(cf); d->meta = c.take<uint32_t>(cf);
+	d->xid = c.take<int32_t>(cf); d->zxid = c.take<int64_t>(cf); d->err = c.take<int32_t>(cf);
+	d->a0 = c.take<int32_t>(cf); d->a1 = c.take<int32_t>(cf);
+	d->czxid = c.take<int64_t>(cs); d->mzxid = c.take<int64_t>(cs);
+	d->ctime = c.take<int64_t>(cs); d->mtime = c.take<int64_t>(cs);
+	d->version = c.take<int32_t>(cs); d->cversion = c.take<int32_t>(cs);
+	d->aversion = c.take<int32_t>(cs); d->ephemeralOwner = c.take<int64_t>(cs);
+	d->dataLength = c.take<int32_t>(cs); d->numChildren = c.take<int32_t>(cs);
+	d->pzxid = c.take<int64_t>(cs);
+	d->buf_rel = c.take<uint32_t>(cb); d->buf_len = c.take<int32_t>(cb);
+	d->acl_perms = c.take<int32_t>(ca);
+	d->sess_consumed = c.take<uint64_t>(nsess); d->sess_bad_length_at = c.take<uint64_t>(nsess);
+	d->sess_first_frame = c.take<uint32_t>((uint64_t)nsess + 1);
+	return c.off;
+}
+
+/* buf_rel, written over the device copy of buf_frame (same index, same thread: no hazard) */
+__global__ void k_buf_rel(zkb_decoded d)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= d.n_buf) return;
+	const uint32_t owner = d.buf_frame[i];
+	d.buf_frame[i] = (uint32_t)(d.buf_off[i] - d.frame_off[owner]);
+}
+
+static int copy_compact_d2h(zkb_ctx *ctx, const zkb_decoded *dv, zkb_decoded *hv, uint32_t nsess)
+{
+#define CP(dst, src, n)                                                                       \
+	if ((n) > 0)                                                                              \
+		ZK_CUDA(ctx, cudaMemcpyAsync(hv->dst, dv->src, (size_t)(n) * sizeof (*hv->dst),           \
+		    cudaMemcpyDeviceToHost, ctx->stream))
+	const uint64_t nf = dv->n_frames, ns = dv->n_stat, nb = dv->n_buf, na = dv->n_acl;
+	CP(frame_len, frame_len, nf); CP(meta, meta, nf); CP(xid, xid, nf); CP(zxid, zxid, nf);
+	CP(err, err, nf); CP(a0, a0, nf); CP(a1, a1, nf);
+	CP(czxid, czxid, ns); CP(mzxid, mzxid, ns); CP(ctime, ctime, ns); CP(mtime, mtime, ns); CP(version, version, ns);
+	CP(cversion, cversion, ns); CP(aversion, aversion, ns); CP(ephemeralOwner, ephemeralOwner, ns);
+	CP(dataLength, dataLength, ns); CP(numChildren, numChildren, ns); CP(pzxid, pzxid, ns);
+	CP(buf_rel, buf_frame, nb); CP(buf_len, buf_len, nb);
+	CP(acl_perms, acl_perms, na);
+	CP(sess_consumed, sess_consumed, nsess); CP(sess_bad_length_at, sess_bad_length_at, nsess);
+	CP(sess_first_frame, sess_first_frame, (uint64_t)nsess + 1);
 #undef CP
 	hv->n_frames = nf; hv->n_stat = ns; hv->n_buf = nb; hv->n_acl = na;
 	return ZKB_OK;
@@ -708,6 +767,10 @@ ZKB_EXPORT int zkb_replay_host(zkb_ctx *ctx,
 			k_rebase<<<(unsigned)(((m1 > n ? m1 : n) + 255) / 256), 256, 0, ctx->stream>>>(dreq, x.req_lo, x.s0, n);
 			k_rebase<<<(unsigned)(((m2 > n ? m2 : n) + 255) / 256), 256, 0, ctx->stream>>>(drsp, x.rsp_lo, x.s0, n);
 			ctx->launches += 2;
+			if (ctx->replay_compact) {
+				if (dreq.n_buf) { k_buf_rel<<<(unsigned)((dreq.n_buf + 255) / 256), 256, 0, ctx->stream>>>(dreq); ctx->launches++; }
+				if (drsp.n_buf) { k_buf_rel<<<(unsigned)((drsp.n_buf + 255) / 256), 256, 0, ctx->stream>>>(drsp); ctx->launches++; }
+			}
 			RP_CUDA(cudaGetLastError());
 			RP_CUDA(cudaEventRecord(ctx->ev_done[b], ctx->stream));
 
@@ -717,10 +780,17 @@ ZKB_EXPORT int zkb_replay_host(zkb_ctx *ctx,
 				cudaStream_t keep = ctx->stream;
 				ctx->stream = ctx->s_out;      /* copy_decoded_d2h queues on ctx->stream */
 				memset(&hreq[b], 0, sizeof (zkb_decoded)); memset(&hrsp[b], 0, sizeof (zkb_decoded));
-				size_t h1 = carve_decoded(&hreq[b], (uint8_t *)ctx->rp_host[b], dreq.n_frames, dreq.n_stat, dreq.n_buf, dreq.n_acl, n);
-				carve_decoded(&hrsp[b], (uint8_t *)ctx->rp_host[b] + zk_align_up(h1, 256), drsp.n_frames, drsp.n_stat, drsp.n_buf, drsp.n_acl, n);
-				rc = copy_decoded_d2h(ctx, &dreq, &hreq[b], n);
-				if (!rc) rc = copy_decoded_d2h(ctx, &drsp, &hrsp[b], n);
+				if (ctx->replay_compact) {
+					size_t h1 = carve_compact(&hreq[b], (uint8_t *)ctx->rp_host[b], dreq.n_frames, dreq.n_stat, dreq.n_buf, dreq.n_acl, n);
+					carve_compact(&hrsp[b], (uint8_t *)ctx->rp_host[b] + zk_align_up(h1, 256), drsp.n_frames, drsp.n_stat, drsp.n_buf, drsp.n_acl, n);
+					rc = copy_compact_d2h(ctx, &dreq, &hreq[b], n);
+					if (!rc) rc = copy_compact_d2h(ctx, &drsp, &hrsp[b], n);
+				} else {
+					size_t h1 = carve_decoded(&hreq[b], (uint8_t *)ctx->rp_host[b], dreq.n_frames, dreq.n_stat, dreq.n_buf, dreq.n_acl, n);
+					carve_decoded(&hrsp[b], (uint8_t *)ctx->rp_host[b] + zk_align_up(h1, 256), drsp.n_frames, drsp.n_stat, drsp.n_buf, drsp.n_acl, n);
+					rc = copy_decoded_d2h(ctx, &dreq, &hreq[b], n);
+					if (!rc) rc = copy_decoded_d2h(ctx, &drsp, &hrsp[b], n);
+				}
 				ctx->stream = keep;
 				if (rc) goto out;
 			}

@@ -79,6 +79,7 @@ struct zkb_ctx {
 	void         *rp_host[2];  size_t rp_host_bytes[2];  /* pinned: slice results */
 	void         *rp_stage[2]; size_t rp_stage_bytes[2]; /* pinned: rebased session arrays */
 	/* optional per-phase CUDA-event timing (zkb_ctx_set_timing) */
+	int           replay_compact; /* zkb_replay_host leaves derivable columns out of the download */
 	int           timing;
 	cudaEvent_t   ev[6];          /* split begin/end, emit begin/end, decode begin/end */
 	float         phase_ms[3];    /* split, emit, decode of the last decode call */

@@ -47,7 +47,7 @@ def test_struct_layouts_match_header(zk):
     a = zk._abi
     assert ctypes.sizeof(a.Sessions) == 32
     assert ctypes.sizeof(a.XidTab) == 40
-    assert ctypes.sizeof(a.Decoded) == 8 * 8 + 8 * (9 + 12 + 3 + 2 + 3)
+    assert ctypes.sizeof(a.Decoded) == 8 * 8 + 8 * (9 + 12 + 3 + 2 + 3 + 1)      # + buf_rel
     assert ctypes.sizeof(a.Requests) == 8 * 26
 
 
@@ -104,3 +104,20 @@ def test_partition_and_merge(zk, synth, oracle):
             bb.append(int(off[s0]))
             sb.append(s0)
         assert shard.merge(cols, bb, sb).diff(full) == []
+
+
+def test_restore_derived_puts_back_what_compact_replay_leaves_out(zk, synth, oracle):
+    """Columns.restore_derived: frame_off, session, the *_frame columns and buf_off rebuilt from the
+    columns a compact replay result still carries, on corpora with damaged frames, empty sessions,
+    handshakes of several depths and every opcode - must equal the full columns."""
+    for corpus in (synth.cfg2_mixed(6, 300, seed=5), synth.fuzz_corpus(11, nsessions=120, max_frames=50),
+                   synth.cfg3_tiny(12, 80), synth.session_corpus(3, 20, 60)):
+        d, off, fl, hs = corpus.arrays()
+        full = oracle.decode(d, off, fl, hs, corpus.xidtable())
+        c = zk.Columns()
+        for k, v in full.__dict__.items():
+            setattr(c, k, v.copy() if isinstance(v, np.ndarray) else v)
+        c.buf_rel = (full.buf_off - full.frame_off[full.buf_frame]).astype(np.uint32)
+        for name in ("frame_off", "session", "stat_frame", "buf_frame", "acl_frame", "buf_off"):
+            setattr(c, name, np.zeros(0, getattr(full, name).dtype))
+        assert c.restore_derived(off).diff(full) == []

@@ -304,6 +304,36 @@ def test_replay_host_pipelined_matches_oracle(ctx, oracle, synth):
     assert (want_rsp.status == 0).all()
 
 
+def test_replay_host_compact_results_restore_to_the_full_columns(zk, oracle, synth):
+    """zkb_ctx_set_replay_compact: the replay leaves frame_off, session, the *_frame columns and buf_off
+    out of the download (buf_rel instead); Columns.restore_derived must rebuild exactly what the full
+    replay delivers, slice by slice, on clean and on damaged traffic."""
+    pc = synth.native_cfg2(77, 21, 1200)
+    n = pc.nsessions
+    rsp = pc.rsp.copy()
+    rsp[int(pc.rsp_off[3]) + 200] ^= 0x40             # some damage: whatever it breaks, both modes must agree
+    layout = zk.XidTable(np.zeros(n, np.int32), np.full(n, pc.frames, np.uint32))
+    c = zk.Context(0)
+    try:
+        for slice_bytes in (0, 400000):
+            full, comp = [], []
+            c.set_replay_compact(False)
+            c.replay_host(pc.req, pc.req_off, rsp, pc.rsp_off, layout.base, layout.count,
+                          lambda first, ns, rq, rs: full.append((first, ns, rq, rs)), slice_bytes=slice_bytes)
+            c.set_replay_compact(True)
+            c.replay_host(pc.req, pc.req_off, rsp, pc.rsp_off, layout.base, layout.count,
+                          lambda first, ns, rq, rs: comp.append((first, ns, rq, rs)), slice_bytes=slice_bytes)
+            assert len(full) == len(comp) and (slice_bytes == 0 or len(full) > 1)
+            for (f0, n0, frq, frs), (f1, n1, crq, crs) in zip(full, comp):
+                assert (f0, n0) == (f1, n1)
+                assert crq.frame_off.size == 0 and crq.buf_off.size == 0 and crq.buf_rel.size == crq.n_buf
+                assert crq.nbytes_columns() < 0.75 * frq.nbytes_columns()
+                assert crq.restore_derived(pc.req_off[f0:f0 + n0 + 1], f0).diff(frq) == []
+                assert crs.restore_derived(pc.rsp_off[f0:f0 + n0 + 1], f0).diff(frs) == []
+    finally:
+        c.close()
+
+
 def test_reencode_round_trip_at_scale(ctx, synth):
     """Config 5's encode half: ~3.2 M requests (830 MB) decoded on the GPU, turned back into
     encode descriptors (RequestBatch.from_columns) and encoded on the GPU must reproduce the wire
