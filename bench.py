@@ -70,18 +70,26 @@ def measured_peak():
     return 6650.0, "fallback 6650 (B200_PROFILING.md)"
 
 
-def pcie_roofline(h2d_gbps_per_gpu, world):
-    """e2e is bound by the upload: fraction of the measured duplex PCIe rate with `world` GPUs of the
-    box copying at once (profiles/pcie_peak_n<world>.json, else the single-GPU profiles/pcie_peak.json)."""
+def pcie_roofline(h2d_bytes, d2h_bytes, seconds, world):
+    """e2e is bound by the host's PCIe complex.  Floor of a step = the larger of (upload bytes at the
+    upload-only rate, download bytes at the download-only rate), both measured with `world` GPUs of
+    the box copying at once (tools/pcie_peak.py -> profiles/pcie_peak_n<world>.json, else the single-GPU
+    profiles/pcie_peak.json): the two directions are assumed to overlap perfectly.  achieved / peak are
+    upload GB/s per GPU, measured and at that floor."""
     for name in ("pcie_peak_n%d.json" % world, "pcie_peak.json"):
         p = os.path.join(ROOT, "profiles", name)
         try:
             with open(p) as f:
-                peak = float(json.load(f)["duplex_h2d_equiv_gbs"])
-            return {"bound": "pcie", "achieved": h2d_gbps_per_gpu, "peak": peak, "unit": "GB/s per GPU (upload)",
-                    "frac": h2d_gbps_per_gpu / peak, "peak_source": "profiles/%s (measured on this pool)" % name}
+                pk = json.load(f)
+            up, down = float(pk["h2d_gbs"]), float(pk["d2h_gbs"])
         except Exception:
             continue
+        floor = max(h2d_bytes / (up * 1e9), d2h_bytes / (down * 1e9))
+        return {"bound": "pcie", "achieved": h2d_bytes / seconds / 1e9, "peak": h2d_bytes / floor / 1e9,
+                "unit": "GB/s per GPU (upload)", "frac": floor / seconds,
+                "limited_by": "upload" if h2d_bytes / up >= d2h_bytes / down else "download",
+                "h2d_peak_gbs": up, "d2h_peak_gbs": down, "gpus_copying": pk.get("n_gpus", 1),
+                "peak_source": "profiles/%s (measured on this pool)" % name}
     return None
 
 
@@ -645,7 +653,7 @@ def run_ours(args, rank, local_rank, world):
                 "api": ("zkb_replay_host" + ("" if args.e2e_full_columns else " (compact results: zkb_ctx_set_replay_compact)"))
                 if wl.paired else "zkb_decode_host",
                 "wire_GBps": total_bytes / (e2e_ms / e2e_steps * 1e-3) / 1e9,
-                "pcie_roofline": pcie_roofline(total_bytes / (e2e_ms / e2e_steps * 1e-3) / 1e9 / max(world, 1), world),
+                "pcie_roofline": pcie_roofline(h2d, d2h, e2e_ms / e2e_steps * 1e-3, world),
                 "host": host_affinity()},
         "gpu_launches": int(launches),
         "split_fixups": ctx.split_fixups,
