@@ -19,13 +19,16 @@
  *                   merges with what is already recorded; scan again; repeat until no granule
  *                   is dirty (one round on ordinary traffic).  By induction from each session
  *                   start the result is then exactly the sequential split.
+ *   k_chunk_meta    two 16-byte records per decode chunk, gathered from the per-granule tables.
  *   k_decode        one warp per 8 KiB chunk (four per CTA): TMA bulk copy of the chunk into
  *                   shared memory; each lane walks the chain through its own 256-byte
- *                   sub-range to place the frame starts; lane k parses frames k, k+32, ... with
- *                   the schema chosen by kind/opcode and writes all FRAMES columns; STAT/BUF/ACL
- *                   rows are recorded as bitmap bits and placed through a decoupled look-back
- *                   over per-chunk row counts, so the input is read from HBM once and the side
- *                   tables come out dense and ordered.
+ *                   sub-range to place the frame starts; lane k reads frames k, k+32, ... in a few
+ *                   converged stages, writes all FRAMES columns and - from the first rows the
+ *                   splitter predicted for the chunk plus one warp scan per round - every STAT /
+ *                   BUF / ACL row where it belongs (zk_decode_direct.cuh).  The input is read from
+ *                   HBM once and the side tables come out dense and ordered.
+ *   k_decode_exact  the exact route for batches in which a frame broke what its header promised:
+ *                   count (bitmap body), k_rows_scan, place - no chunk waits for another.
  */
 #include <stdlib.h>
 
@@ -353,7 +356,7 @@ __device__ uint64_t guess_entry(const SplitArgs &a, uint32_t s, uint64_t gs, uin
  * walk adds these up per granule, the scan turns them into each decode chunk's first row, and
  * k_decode<true> places its rows there without waiting for its predecessors; it compares what
  * it really found with the prediction, and a single mismatch (a malformed frame, a handshake
- * depth the walk cannot know) makes the host repeat the pass with the look-back.  So this is a
+ * depth the walk cannot know) makes the host place the rest of the batch by the exact route.  So this is a
  * guess that costs time when wrong, never a wrong answer. */
 struct RowCnt { uint32_t st, bf, ac; };
 
@@ -1001,7 +1004,7 @@ __device__ __forceinline__ bool c_stat(Cur &c, uint32_t &pos)
 	return false;
 }
 
-/* what one frame contributes; small enough to live in registers across the look-back */
+/* what one frame contributes */
 struct Parsed {
 	uint32_t meta;
 	int32_t  xid, err, a0, a1;
@@ -1656,20 +1659,12 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane)
 	return v;
 }
 
-#define ZK_SPIN_LIMIT (1u << 26)
-#ifndef ZK_SLEEP_MIN
-#define ZK_SLEEP_MIN 128u   /* ns; the look-back's poll interval doubles from here ... */
-#endif
-#ifndef ZK_SLEEP_MAX
-#define ZK_SLEEP_MAX 1024u  /* ... to here */
-#endif
-
 /* Build with -DZK_PROFILE_PHASES to accumulate, per chunk, the SM cycles a decode warp spends
- * in each phase (ticket, staging wait, frame loop, counts, look-back, emission) into
+ * in each phase (ticket, staging wait, frame loop, counts, placement, emission) of the exact body into
  * zk_ctrl::prof; read them with zkb_debug_phase_cycles().  Off in normal builds. */
 #ifdef ZK_PROFILE_PHASES
 /* histogram of cycles from tile issue to AGG publish (1024-cycle buckets), chunks without /
- * with generic-parser frames; and of the look-back wait */
+ * with generic-parser frames */
 __device__ unsigned long long zk_hist[3][64];
 #define ZK_T(i) const long long zk_t##i = clock64()
 #define ZK_ACC(slot, a, b) do { if (lane == 0) atomicAdd(&a_ctrl_prof[slot], (unsigned long long)((b) - (a))); } while (0)

@@ -20,16 +20,10 @@
 #define ZK_NONE     0xFFFFFFFFFFFFFFFFull  /* no live chain */
 #define ZK_INHERIT  0xFFFFFFFFFFFFFFFEull  /* granule did not touch the chain */
 
-/* look-back flags */
-#define ZK_LB_EMPTY 0u
-#define ZK_LB_AGG   1u
-#define ZK_LB_PFX   2u
-
 /* device error bits (d_ctrl->error) */
 #define ZK_DERR_SESSIONS  1u  /* session offsets not monotone / not covering the batch */
-#define ZK_DERR_LOOKBACK  2u  /* look-back spin limit hit (would have been a hang) */
 #define ZK_DERR_COUNT     4u  /* frame count disagreed between split and emit */
-#define ZK_DERR_MISPREDICT 8u /* a chunk's side rows differ from the splitter's prediction: redo with the look-back */
+#define ZK_DERR_MISPREDICT 8u /* a chunk's side rows differ from the splitter's prediction: place the rest by the exact route */
 
 struct zk_ctrl {
 	unsigned int       error;
@@ -53,10 +47,10 @@ struct zkb_ctx {
 	uint64_t      launches;
 	uint64_t      split_fixups;   /* FIX iterations the splitter has needed so far */
 	uint64_t      slow_frames;    /* frames the last decode sent through the generic parser */
-	int           no_predict;     /* ZKBATCH_NO_PREDICT=1: always place side rows by look-back */
+	int           no_predict;     /* ZKBATCH_NO_PREDICT=1: every batch takes the exact route (count, scan, place) */
 	int           dir;            /* batch split last: 1 = only client->server streams, 2 = only server->client, 0 = both */
 	uint64_t      pred_rows[3];   /* predicted side-table rows of the batch split last (exact for well-formed traffic) */
-	uint64_t      mispredicts;    /* decode passes repeated with the look-back because a row prediction failed */
+	uint64_t      mispredicts;    /* batches whose tail was placed again by the exact route because a row prediction failed */
 	unsigned long long prof[8];
 	unsigned long long split_prof[8];
 	unsigned int split_iters[32][2];  /* last split: (n_dirty, n_rewalk) after each scan */

@@ -51,8 +51,8 @@ for seed in range(first, first + count):
                 else:
                     names.append(bytes(rng.getrandbits(8) for _ in range(rng.choice([0, 1, 3, 5, 300, 700]) if r < 0.2 else rng.randrange(1, 20))))
             op = rng.choice([8, 12, 12])
-            count = n + rng.choice([0, 0, 0, 1, -1, -n - 3, 5])
-            body = synth.resp_header(i, 9 + i, rng.choice([0, 0, 0, -101])) + synth.be32(count)
+            claimed = n + rng.choice([0, 0, 0, 1, -1, -n - 3, 5])
+            body = synth.resp_header(i, 9 + i, rng.choice([0, 0, 0, -101])) + synth.be32(claimed)
             body += b"".join(struct.pack(">i", len(x) if x or rng.random() < 0.5 else -1) + x for x in names)
             if op == 12:
                 body += synth.stat_bytes(rng, 0, n)
