@@ -461,3 +461,47 @@ def test_long_children_vectors_adversarial(ctx, oracle, synth):
     g, o = both(ctx, oracle, c)
     assert g.diff(o) == []
     assert (o.status == 1).sum() >= 1 and g.n_buf > 15000
+
+
+def test_crowded_chunks(ctx, oracle, synth):
+    """More frames in one 8 KiB chunk than the decode kernel's frame list holds (400), and more
+    vector frames than its work list (64): thousands of zero-length frames (legal length, BAD_DECODE
+    each), 8-byte frames, and hundreds of tiny GET_CHILDREN / GET_CHILDREN2 / GET_ACL replies with
+    0-2 elements back to back, in both directions, with ordinary frames mixed in."""
+    import random
+    rng = random.Random(7)
+    c = synth.Corpus()
+    # replies: runs of empty frames, then tiny vector replies
+    parts, xm, xid = [synth.frame(synth.connect_response(rng))], {}, 0
+    parts += [synth.frame(b"")] * 3000
+    for _ in range(2500):
+        op = rng.choice([8, 12, 6, 8, 12])
+        n = rng.randrange(0, 3)
+        if op == 6:
+            body = synth.acl_bytes([(rng.randrange(32), b"s", b"i%d" % k) for k in range(n)]) + synth.stat_bytes(rng)
+        else:
+            body = synth.be32(n) + b"".join(synth.jbuf(b"c%d" % k) for k in range(n))
+            if op == 12:
+                body += synth.stat_bytes(rng, 0, n)
+        parts.append(synth.frame(synth.resp_header(xid, xid + 5, 0) + body))
+        xm[xid] = op
+        xid += 1
+        if rng.random() < 0.3:
+            parts.append(synth.frame(synth.resp_header(-2, 1, 0)))
+        if rng.random() < 0.05:
+            parts += [synth.frame(b"")] * rng.randrange(1, 700)
+    c.add(b"".join(parts), xidmap=xm)
+    # requests: 8-byte frames (xid + PING / CLOSE_SESSION: 'Unsupported opcode'), CREATEs with 0-3 ACL entries
+    parts = [synth.frame(synth.connect_request(rng))]
+    for i in range(4000):
+        r = rng.random()
+        if r < 0.7:
+            parts.append(synth.frame(synth.be32(-2) + synth.be32(rng.choice([11, -11]))))
+        else:
+            ents = [(rng.randrange(32), b"world", b"anyone")] * rng.randrange(0, 4)
+            parts.append(synth.frame(synth.be32(i) + synth.be32(1) + synth.jbuf(b"/p") + synth.jbuf(b"") +
+                                     synth.acl_bytes(ents) + synth.be32(rng.randrange(4))))
+    c.add(b"".join(parts), server=True)
+    g, o = both(ctx, oracle, c)
+    assert g.diff(o) == []
+    assert g.n_frames > 12000 and (g.status == 1).sum() > 5000
