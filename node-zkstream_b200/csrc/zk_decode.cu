@@ -586,8 +586,11 @@ __device__ __forceinline__ bool fix_trusted(const SplitArgs &a, uint32_t g)
 #define ZK_FIX_EXT 64   /* granules one fix-up thread may carry its corrected chain through */
 #endif
 
+#ifndef ZK_SPLIT_MINBLOCKS
+#define ZK_SPLIT_MINBLOCKS 1
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(128) k_split(SplitArgs a)
+__global__ void __launch_bounds__(128, ZK_SPLIT_MINBLOCKS) k_split(SplitArgs a)
 {
 	uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
 	if (g >= a.n_gran) return;
