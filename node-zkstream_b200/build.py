@@ -13,7 +13,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libzkbatch.so")
 SOURCES = ["zk_ctx.cu", "zk_decode.cu", "zk_encode.cu", "zk_stats.cu"]
-HEADERS = [os.path.join(CSRC, "zk_internal.h"), os.path.join(HERE, "..", "include", "zkbatch.h")]
+HEADERS = [os.path.join(CSRC, "zk_internal.h"), os.path.join(CSRC, "zk_decode_direct.cuh"),
+           os.path.join(HERE, "..", "include", "zkbatch.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

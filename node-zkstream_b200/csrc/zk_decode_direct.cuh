@@ -134,28 +134,78 @@ __device__ __forceinline__ void put_stat(const zkb_decoded &o, const uint8_t *ti
 }
 
 /* Walk the vectors set aside so far, one lane per frame.  Returns false in a lane whose frame did
- * not keep what its header promised. */
+ * not keep what its header promised.
+ *
+ * LAST: the chunk's last drain.  The frame list is no longer needed then, so its memory takes the
+ * tile offsets of the string elements: each lane walks its own vector reading lengths only, and all
+ * lanes together write the rows afterwards (one element per lane, whichever vector it belongs to).
+ * The entries of the batch at hand have been read into registers by then, so their memory holds
+ * what the second phase needs to find an element's vector: one bit per element that opens a vector,
+ * and { first row - first list slot, frame } of every vector that has elements. */
+template <bool LAST>
 __device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, const uint64_t cs, const uint32_t f0,
     const uint32_t e0, const uint32_t e1, const uint32_t e2, const uint32_t nv, const uint32_t lane)
 {
 	const zkb_decoded &o = a.o;
+	uint16_t *list = c.frel;
+	uint2 *vinfo = reinterpret_cast<uint2 *>(c.vl);                       /* 32 x 8 bytes */
+	uint32_t *heads = reinterpret_cast<uint32_t *>(c.vl + 16);            /* ZK_FREL_CAP bits */
 	bool good = true;
-	for (uint32_t i = lane; i < nv; i += 32) {
-		const VEnt e = c.vl[i];
+	for (uint32_t i0 = 0; i0 < nv; i0 += 32) {
+		const uint32_t i = i0 + lane;
+		const bool have = i < nv;
+		VEnt e;
+		e.w0 = 4u; e.w1 = e.w2 = e.w3 = 0u;
+		if (have) e = c.vl[i];
 		const uint32_t pr = e.w0 & 0xffffu, vrel = e.w0 >> 16;
 		uint32_t brow = e1 + (e.w1 & 0xffffu), arow = e2 + (e.w1 >> 16);
 		const uint32_t srow = e0 + (e.w2 & 0xffffu), kind = e.w2 >> 16;
 		const uint32_t frame = f0 + e.w3;
 		const uint32_t end = pr + sm_be32(c.tile, pr - 4);          /* tile offset one past the payload */
-		const int32_t count = (int32_t)sm_be32(c.tile, vrel);
+		const int32_t count = have ? (int32_t)sm_be32(c.tile, vrel) : 0;
 		uint32_t cur = vrel + 4;
 		bool ok = true;
 		const uint64_t base = cs + 4;
 		const uint64_t want = count > 0 ? (uint64_t)count : 0u;
-		if (kind == VK_STR || kind == VK_STR_STAT) {
-			/* vector<ustring> (zk-buffer.js:334-337).  An element's length is read even when fewer
-			 * than four bytes are left (the tile is zero padded): the end test below catches it. */
-			if (brow + want <= o.cap_buf) {
+		const bool str = have && (kind == VK_STR || kind == VK_STR_STAT);
+		const bool fits = brow + want <= o.cap_buf;
+		/* ---- which vectors go through the list ---- */
+		bool listed = false;
+		uint32_t slot = 0, total = 0;
+		if (LAST) {
+			const uint32_t n2 = (str && fits) ? (uint32_t)(want < ZK_FREL_CAP + 1u ? want : ZK_FREL_CAP + 1u) : 0u;
+			const uint32_t inc = warp_incl_scan(n2, lane);
+			total = __shfl_sync(0xffffffffu, inc, 31);
+			if (total > ZK_FREL_CAP) total = 0;              /* too many elements for the list: lane by lane */
+			const uint32_t nonempty = __ballot_sync(0xffffffffu, n2 != 0);
+			__syncwarp();                                    /* every entry of the batch is in registers */
+			if (total) {
+				slot = inc - n2;
+				listed = n2 != 0;
+				if (lane < (ZK_FREL_CAP + 31u) / 32u) heads[lane] = 0;
+				if (listed) vinfo[__popc(nonempty & ((1u << lane) - 1u))] = make_uint2(brow - slot, frame);
+				__syncwarp();
+				if (listed) atomicOr(&heads[slot >> 5], 1u << (slot & 31u));
+			}
+		}
+		if (listed) {
+			/* phase one: lengths only (vector<ustring>, zk-buffer.js:334-337).  An element's length is
+			 * read even when fewer than four bytes are left (the tile is zero padded): the end test
+			 * catches it. */
+			const uint32_t n = (uint32_t)want;
+			uint32_t k = 0;
+			for (; k < n; ++k) {
+				const int32_t l = (int32_t)sm_be32(c.tile, cur);
+				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+				const uint32_t nxt = cur + 4 + ul;
+				if (nxt > end) break;
+				list[slot + k] = (uint16_t)cur;
+				cur = nxt;
+			}
+			ok = k >= n;
+			for (; k < n; ++k) list[slot + k] = 0xFFFFu;         /* the count lied: no rows for the rest */
+		} else if (str) {
+			if (fits) {
 				uint32_t *pf = o.buf_frame + brow; uint64_t *po = o.buf_off + brow; int32_t *pl = o.buf_len + brow;
 				int32_t k = 0;
 				for (; k < count; ++k) {
@@ -177,9 +227,9 @@ __device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, cons
 					cur += 4 + ul;
 				}
 			}
-		} else {
+		} else if (have) {
 			/* readACL (zk-buffer.js:372-382): count x { perms, scheme, id } */
-			const bool fits = brow + 2 * want <= o.cap_buf && arow + want <= o.cap_acl;
+			const bool afits = brow + 2 * want <= o.cap_buf && arow + want <= o.cap_acl;
 			for (int32_t k = 0; k < count; ++k) {
 				const int32_t perms = (int32_t)sm_be32(c.tile, cur);
 				const int32_t l0 = (int32_t)sm_be32(c.tile, cur + 4);
@@ -189,7 +239,7 @@ __device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, cons
 				const int32_t l1 = (int32_t)sm_be32(c.tile, c1);
 				const uint32_t u1 = l1 > 0 ? (uint32_t)l1 : 0u;
 				if (c1 + 4 + u1 > end) { ok = false; break; }
-				if (fits) {
+				if (afits) {
 					o.acl_frame[arow] = frame; o.acl_perms[arow] = perms;
 					o.buf_frame[brow] = frame; o.buf_off[brow] = base + cur + 4; o.buf_len[brow] = (int32_t)u0;
 					o.buf_frame[brow + 1] = frame; o.buf_off[brow + 1] = base + c1; o.buf_len[brow + 1] = (int32_t)u1;
@@ -202,7 +252,29 @@ __device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, cons
 				cur = c1 + 4 + u1;
 			}
 		}
-		if (ok) {
+		__syncwarp();
+		if (LAST && total) {
+			/* phase two: element j of the list belongs to the vector whose opening bit is the last one
+			 * at or below j */
+			uint32_t before = 0;
+			for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+				const uint32_t hw = heads[j0 >> 5];
+				const uint32_t j = j0 + lane;
+				if (j < total) {
+					const uint2 vi = vinfo[before + __popc(hw & (0xffffffffu >> (31u - lane))) - 1u];
+					const uint32_t p = list[j];
+					if (p != 0xFFFFu) {
+						const int32_t l = (int32_t)sm_be32(c.tile, p);
+						const uint32_t row = vi.x + j;
+						o.buf_frame[row] = vi.y; o.buf_off[row] = base + p; o.buf_len[row] = l > 0 ? l : 0;
+					}
+				}
+				before += __popc(hw);
+			}
+			__syncwarp();
+		}
+		/* what follows the vector, all lanes together */
+		if (have && ok) {
 			if (kind == VK_ACL_FLAGS) {                      /* CREATE request: flags follow the ACL */
 				if (cur + 4 > end) ok = false;
 				else a.o.a0[frame] = (int32_t)sm_be32(c.tile, cur);
@@ -637,7 +709,7 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 		for (uint32_t k0 = wlo; k0 < wend; k0 += 32) {
 			if (nv > ZK_VL_CAP - 32) {
 				__syncwarp();
-				good = drain_vectors(a, c, cs, f0, e0, e1, e2, nv, lane) && good;
+				good = drain_vectors<false>(a, c, cs, f0, e0, e1, e2, nv, lane) && good;
 				nv = 0;
 				__syncwarp();
 			}
@@ -751,7 +823,11 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 		__syncwarp();
 	} while (wlo < nfr);
 	__syncwarp();
-	if (nv) good = drain_vectors(a, c, cs, f0, e0, e1, e2, nv, lane) && good;
+		/* request streams carry no string vectors (the ACL of a CREATE is walked lane by lane) */
+#ifndef ZK_DRAIN_LIST
+#define ZK_DRAIN_LIST (DIR != 1)
+#endif
+	if (nv) good = drain_vectors<ZK_DRAIN_LIST>(a, c, cs, f0, e0, e1, e2, nv, lane) && good;
 	good = __all_sync(0xffffffffu, good);
 	n_slow = warp_sum(n_slow);
 	if (lane == 0 && n_slow) atomicAdd(&a.ctrl->n_slow, (unsigned long long)n_slow);
