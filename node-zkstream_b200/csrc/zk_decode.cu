@@ -375,7 +375,7 @@ __device__ __forceinline__ Hdr load_hdr(const uint8_t *bytes, uint64_t pos, uint
 {
 	Hdr h;
 	const uint64_t base = pos & ~3ull;
-	const uint32_t sh = (uint32_t)(pos & 3) * 8;
+	const uint32_t sel = 0x0123u + 0x1111u * (uint32_t)(pos & 3);    /* byte permute: four bytes, most significant first */
 	const uint32_t *p = reinterpret_cast<const uint32_t *>(bytes + base);
 	uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0, x5 = 0, x6 = 0;
 	if (base + 28 <= padend) {
@@ -390,12 +390,12 @@ __device__ __forceinline__ Hdr load_hdr(const uint8_t *bytes, uint64_t pos, uint
 		if (base + 20 <= padend) x4 = __ldg(p + 4);
 		if (base + 24 <= padend) x5 = __ldg(p + 5);
 	}
-	h.len = bswap32(__funnelshift_r(x0, x1, sh));
-	h.w1 = bswap32(__funnelshift_r(x1, x2, sh));
-	h.w2 = bswap32(__funnelshift_r(x2, x3, sh));
-	h.w3 = bswap32(__funnelshift_r(x3, x4, sh));
-	h.w4 = bswap32(__funnelshift_r(x4, x5, sh));
-	h.w5 = bswap32(__funnelshift_r(x5, x6, sh));
+	h.len = __byte_perm(x0, x1, sel);
+	h.w1 = __byte_perm(x1, x2, sel);
+	h.w2 = __byte_perm(x2, x3, sel);
+	h.w3 = __byte_perm(x3, x4, sel);
+	h.w4 = __byte_perm(x4, x5, sel);
+	h.w5 = __byte_perm(x5, x6, sel);
 	return h;
 }
 
@@ -923,7 +923,7 @@ struct Rd {
 		uint64_t r = pos - lo;
 		if (r + 4 <= (uint64_t)wlen) {
 			const uint32_t *w = reinterpret_cast<const uint32_t *>(sm + ((uint32_t)r & ~3u));
-			return bswap32(__funnelshift_r(w[0], w[1], ((uint32_t)r & 3u) * 8));
+			return __byte_perm(w[0], w[1], 0x0123u + 0x1111u * ((uint32_t)r & 3u));
 		}
 		return g_be32(g, pos);
 	}
@@ -1075,8 +1075,9 @@ enum { FAST_MARK = 1, FAST_UNMARK = 2 };
 
 __device__ __forceinline__ uint32_t sm_be32(const uint8_t *tile, uint32_t rel)
 {
+	/* one byte permute picks the four bytes, most significant first, out of the two aligned words */
 	const uint32_t *w = reinterpret_cast<const uint32_t *>(tile + (rel & ~3u));
-	return bswap32(__funnelshift_r(w[0], w[1], (rel & 3u) * 8));
+	return __byte_perm(w[0], w[1], 0x0123u + 0x1111u * (rel & 3u));
 }
 
 template <int M>

@@ -116,13 +116,13 @@ __device__ __forceinline__ void put_stat(const zkb_decoded &o, const uint8_t *ti
 	if (row >= o.cap_stat) return;
 	/* 68 bytes = 17 big-endian words from 18 aligned shared-memory words */
 	const uint32_t *wp = reinterpret_cast<const uint32_t *>(tile + (q & ~3u));
-	const uint32_t sh = (q & 3u) * 8;
+	const uint32_t sel = 0x0123u + 0x1111u * (q & 3u);
 	uint32_t x[18];
 #pragma unroll
 	for (int i = 0; i < 18; ++i) x[i] = wp[i];
 	uint32_t v[17];
 #pragma unroll
-	for (int i = 0; i < 17; ++i) v[i] = bswap32(__funnelshift_r(x[i], x[i + 1], sh));
+	for (int i = 0; i < 17; ++i) v[i] = __byte_perm(x[i], x[i + 1], sel);
 #define Q64(i) ((int64_t)(((uint64_t)v[i] << 32) | (uint64_t)v[(i) + 1]))
 	o.stat_frame[row] = frame;
 	o.czxid[row] = Q64(0); o.mzxid[row] = Q64(2); o.ctime[row] = Q64(4); o.mtime[row] = Q64(6);
@@ -192,18 +192,17 @@ __device__ __forceinline__ bool drain_vectors(const DecArgs &a, ChunkSm &c, cons
 			/* phase one: lengths only (vector<ustring>, zk-buffer.js:334-337).  An element's length is
 			 * read even when fewer than four bytes are left (the tile is zero padded): the end test
 			 * catches it. */
-			const uint32_t n = (uint32_t)want;
-			uint32_t k = 0;
-			for (; k < n; ++k) {
+			uint16_t *lp = list + slot;
+			uint16_t *const le = lp + (uint32_t)want;
+			while (lp < le) {
 				const int32_t l = (int32_t)sm_be32(c.tile, cur);
-				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
-				const uint32_t nxt = cur + 4 + ul;
+				const uint32_t nxt = cur + 4 + (uint32_t)max(l, 0);
 				if (nxt > end) break;
-				list[slot + k] = (uint16_t)cur;
+				*lp++ = (uint16_t)cur;
 				cur = nxt;
 			}
-			ok = k >= n;
-			for (; k < n; ++k) list[slot + k] = 0xFFFFu;         /* the count lied: no rows for the rest */
+			ok = lp == le;
+			while (lp < le) *lp++ = 0xFFFFu;                     /* the count lied: no rows for the rest */
 		} else if (str) {
 			if (fits) {
 				uint32_t *pf = o.buf_frame + brow; uint64_t *po = o.buf_off + brow; int32_t *pl = o.buf_len + brow;
@@ -352,17 +351,21 @@ __device__ __forceinline__ bool direct_request(const uint8_t *t, const uint32_t 
 }
 
 /* readResponse (zk-buffer.js:281-331) for a frame inside the tile */
+/* the xid table's entry of one session, fetched while the tile is on its way */
+struct XidSess { uint32_t s; int32_t base; uint32_t count; uint64_t off; };
+
 __device__ __forceinline__ bool direct_response(const uint8_t *t, const DecArgs &a, const uint32_t pr, const uint32_t size,
-    const uint32_t s, FrameCols &o, Fr &fr)
+    const uint32_t s, const XidSess &xs, FrameCols &o, Fr &fr)
 {
 	if (size < 16) return false;
 	const int32_t xid = (int32_t)sm_be32(t, pr);
 	const int32_t err = (int32_t)sm_be32(t, pr + 12);
 	int op = special_xid(xid);
 	if (op == ZKB_OP_NONE && a.xt_ops) {
-		const int64_t idx = (int64_t)xid - (int64_t)__ldg(a.xt_base + s);
-		if (idx >= 0 && idx < (int64_t)__ldg(a.xt_count + s))
-			op = __ldg(a.xt_ops + __ldg(a.xt_off + s) + (uint64_t)idx);
+		const bool pre = (s == xs.s);
+		const int64_t idx = (int64_t)xid - (int64_t)(pre ? xs.base : __ldg(a.xt_base + s));
+		if (idx >= 0 && idx < (int64_t)(pre ? xs.count : __ldg(a.xt_count + s)))
+			op = __ldg(a.xt_ops + (pre ? xs.off : __ldg(a.xt_off + s)) + (uint64_t)idx);
 	}
 	if (op == ZKB_OP_NONE) return false;                 /* 'reply packet must match a request' */
 	o.xid = xid; o.err = err; o.a0 = 0; o.a1 = 0;
@@ -662,6 +665,13 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 			else { es = sprev + 1; esend = b_next; e_start = true; }
 		}
 	}
+	/* replies: the xid table's entry of the session the chunk starts in */
+	XidSess xs;
+	xs.s = 0xFFFFFFFFu; xs.base = 0; xs.count = 0; xs.off = 0;
+	if (DIR != 1 && a.xt_ops && cont) {
+		xs.s = sf - 1;
+		xs.base = __ldg(a.xt_base + xs.s); xs.count = __ldg(a.xt_count + xs.s); xs.off = __ldg(a.xt_off + xs.s);
+	}
 	__syncwarp();
 	mbar_wait(bar, 0);
 
@@ -760,7 +770,7 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 				bool done = false;
 				if (inwin && idx >= hs)
 					done = server ? direct_request(c.tile, rel + 4, (uint32_t)flen, o, fr)
-					              : direct_response(c.tile, a, rel + 4, (uint32_t)flen, s, o, fr);
+					              : direct_response(c.tile, a, rel + 4, (uint32_t)flen, s, xs, o, fr);
 				if (!done && !inwin && !server && idx >= hs &&
 				    direct_response_long(c, a, rel + 4, (uint32_t)flen, wlen, s, o)) {
 					done = true;
