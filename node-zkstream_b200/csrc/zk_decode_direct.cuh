@@ -674,6 +674,14 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 	}
 	__syncwarp();
 	mbar_wait(bar, 0);
+	/* replies: ask for the xid table's bytes now - the first frames of every eighth sub-range span the
+	 * chunk's xids closely enough - so the header stage finds them in cache (a wrong or special xid asks
+	 * for nothing) */
+	if (DIR != 1 && (lane & 7u) == 0 && xs.s != 0xFFFFFFFFu && entry != ZK_NONE && (uint32_t)(entry - cs) + 8u <= wlen) {
+		const int64_t idx = (int64_t)(int32_t)sm_be32(c.tile, (uint32_t)(entry - cs) + 4u) - (int64_t)xs.base;
+		if (idx >= 0 && idx < (int64_t)xs.count)
+			asm volatile("prefetch.global.L1 [%0];" :: "l"(a.xt_ops + xs.off + (uint64_t)idx));
+	}
 
 	/* ---- frame starts: count per lane, prefix over lanes.  A lane whose sub-range is a plain run of
 	 * frames keeps their offsets in registers; the others (a session ends or starts there, a bad or
