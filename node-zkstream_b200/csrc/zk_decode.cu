@@ -741,9 +741,12 @@ __device__ ScanVal block_scan_incl(ScanVal x, ScanVal *total, ScanVal *s_w /* [3
 	return sv_comb(pre, x);
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanVal *blk)
+/* `gate`: the scan that follows the queued fix-up round has nothing to do when the first scan found
+ * every granule consistent (request streams, ordinarily): NULL = always run, else run iff *gate != 0 */
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanVal *blk, const unsigned int *gate)
 {
 	__shared__ ScanVal s_w[32];
+	if (gate && *gate == 0) return;
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
 	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.r0 = x.r1 = x.r2 = 0;
 	if (g < a.n_gran) {
@@ -760,9 +763,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(SplitArgs a, ScanV
 }
 
 /* exclusive scan of the block aggregates, in place, by one block */
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint32_t nblk)
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint32_t nblk, const unsigned int *gate)
 {
 	__shared__ ScanVal s_w[32];
+	if (gate && *gate == 0) return;
 	ScanVal carry; carry.v = ZK_INHERIT; carry.c = 0; carry.src = 0; carry.ssrc = 0; carry.r0 = carry.r1 = carry.r2 = 0;
 	for (uint32_t b0 = 0; b0 < nblk; b0 += SCAN_THREADS) {
 		uint32_t i = b0 + threadIdx.x;
@@ -785,10 +789,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_blocks(ScanVal *blk, uint
 	}
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const ScanVal *blk)
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(SplitArgs a, const ScanVal *blk, const unsigned int *gate)
 {
 	__shared__ ScanVal s_w[32];
 	__shared__ ScanVal s_last[32];
+	if (gate && *gate == 0) return;
 	uint32_t g = blockIdx.x * SCAN_THREADS + threadIdx.x;
 	ScanVal x; x.v = ZK_INHERIT; x.c = 0; x.src = 0; x.ssrc = 0; x.r0 = x.r1 = x.r2 = 0;
 	if (g < a.n_gran) {
@@ -2209,6 +2214,62 @@ __global__ void k_xid_scatter(const zkb_decoded req, uint64_t n_frames, uint32_t
 	atomicMax(tmp + slot, key);
 }
 
+/* The same without atomics, for the ordinary case that no two requests of a connection share an
+ * xid: every request stores its opcode byte, and the stores are counted.  If afterwards as many
+ * slots hold an opcode as requests stored one, no slot was written twice and the table is exact;
+ * otherwise the caller runs the ordered build above. */
+__global__ void __launch_bounds__(256) k_xid_store(const zkb_decoded req, uint64_t n_frames, uint32_t nsess,
+    const int32_t *base, const uint32_t *count, const uint64_t *off, int8_t *ops, uint64_t nops, zk_ctrl *ctrl)
+{
+	__shared__ uint32_t s_n;
+	if (threadIdx.x == 0) s_n = 0;
+	__syncthreads();
+	uint32_t mine = 0;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t f = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; f < n_frames; f += stride) {
+		const uint32_t m = req.meta[f];
+		if (ZKB_META_KIND(m) != ZKB_KIND_REQUEST || req.frame_len[f] < 8) continue;
+		const uint32_t s = req.session[f];
+		if (s >= nsess) continue;
+		const int64_t idx = (int64_t)req.xid[f] - (int64_t)base[s];
+		if (idx < 0 || idx >= (int64_t)count[s]) continue;
+		const uint64_t slot = off[s] + (uint64_t)idx;
+		if (slot >= nops) continue;       /* a layout entry that points past the table is dropped, as above */
+		ops[slot] = (int8_t)((m >> 8) & 0xff);
+		mine++;
+	}
+	for (int d = 16; d > 0; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+	if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&s_n, mine);
+	__syncthreads();
+	if (threadIdx.x == 0 && s_n) atomicAdd(&ctrl->xid_stored, (unsigned long long)s_n);
+}
+
+/* slots that hold an opcode (anything but ZKB_OP_NONE), 16 per thread */
+__global__ void __launch_bounds__(256) k_xid_filled(const int8_t *ops, uint64_t nops, zk_ctrl *ctrl)
+{
+	__shared__ uint32_t s_n;
+	if (threadIdx.x == 0) s_n = 0;
+	__syncthreads();
+	uint32_t c = 0;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x * 16;
+	const bool aligned = ((uintptr_t)ops & 15) == 0;
+	for (uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < nops; i += stride) {
+		if (aligned && i + 16 <= nops) {
+			const uint4 v = *reinterpret_cast<const uint4 *>(ops + i);
+			const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+			for (int k = 0; k < 4; ++k)
+				c += 4u - (__popc(__vcmpeq4(w[k], 0x80808080u)) >> 3);     /* 0xff per byte that is ZKB_OP_NONE */
+		} else {
+			for (uint64_t k = i; k < nops && k < i + 16; ++k) c += ops[k] != (int8_t)ZKB_OP_NONE;
+		}
+	}
+	for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+	if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_n, c);
+	__syncthreads();
+	if (threadIdx.x == 0 && s_n) atomicAdd(&ctrl->xid_filled, (unsigned long long)s_n);
+}
+
 __global__ void k_xid_finish(const unsigned long long *tmp, uint64_t n, int8_t *ops)
 {
 	uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -2356,11 +2417,13 @@ int zk_split_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	/* Ordinary traffic needs exactly one fix-up round, so SPEC, scan, FIX, scan are queued back to back
 	 * and the host looks at the result once; FIX returns at once in granules that are not dirty. */
 	for (uint32_t iter = 0;; ++iter) {
-		k_scan_reduce<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk);
+		/* the scan queued behind the first fix-up round runs only if the first scan left anything to fix */
+		const unsigned int *gate = (iter == 1) ? &ctx->d_ctrl->first_dirty[0] : NULL;
+		k_scan_reduce<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk, gate);
 		LAUNCH_CHECK(ctx);
-		k_scan_blocks<<<1, SCAN_THREADS, 0, ctx->stream>>>(blk, L.n_blk);
+		k_scan_blocks<<<1, SCAN_THREADS, 0, ctx->stream>>>(blk, L.n_blk, gate);
 		LAUNCH_CHECK(ctx);
-		k_scan_apply<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk);
+		k_scan_apply<<<L.n_blk, SCAN_THREADS, 0, ctx->stream>>>(sa, blk, gate);
 		LAUNCH_CHECK(ctx);
 		if (iter == 0) {
 			k_split_round<<<1, 1, 0, ctx->stream>>>(ctx->d_ctrl);
@@ -2574,6 +2637,20 @@ int zk_xidtab_build_device(zkb_ctx *ctx, const zkb_decoded *req, uint32_t nsessi
 	if (!req || !layout || !d_ops_out) return ZKB_EINVAL;
 	const uint64_t n = layout->nops;
 	if (n == 0) return ZKB_OK;
+	/* first without atomics; exact unless two requests of a connection share an xid */
+	ZK_CUDA(ctx, cudaMemsetAsync(d_ops_out, (int)(uint8_t)(int8_t)ZKB_OP_NONE, n, ctx->stream));
+	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->xid_stored, 0, 2 * sizeof (unsigned long long), ctx->stream));
+	if (req->n_frames) {
+		const uint64_t want_s = (req->n_frames + 255) / 256, want_f = (n + 4095) / 4096;
+		k_xid_store<<<(unsigned)(want_s < 148 * 32 ? want_s : 148 * 32), 256, 0, ctx->stream>>>(*req,
+		    req->n_frames, nsessions, layout->base, layout->count, layout->off, d_ops_out, n, ctx->d_ctrl);
+		LAUNCH_CHECK(ctx);
+		k_xid_filled<<<(unsigned)(want_f < 148 * 16 ? want_f : 148 * 16), 256, 0, ctx->stream>>>(d_ops_out, n, ctx->d_ctrl);
+		LAUNCH_CHECK(ctx);
+	}
+	if ((rc = zk_read_ctrl(ctx))) return rc;
+	if (ctx->h_ctrl->xid_stored == ctx->h_ctrl->xid_filled) return ZKB_OK;
+	/* some slot was written more than once: the last request in stream order must win */
 	if ((rc = zk_ensure(ctx, &ctx->d_scratch, &ctx->d_scratch_bytes, n * 8 + 256, 0))) return rc;
 	unsigned long long *tmp = (unsigned long long *)ctx->d_scratch;
 	ZK_CUDA(ctx, cudaMemsetAsync(tmp, 0, n * 8, ctx->stream));

@@ -38,6 +38,7 @@ struct zk_ctrl {
 	unsigned int       pred_rows[3]; /* the splitter's predicted STAT / BUF / ACL row totals of the batch */
 	unsigned int       dir_mask;     /* 1 = some session is client->server, 2 = some is server->client (k_check_sessions) */
 	unsigned int       first_dirty[2]; /* n_dirty / n_rewalk after the first scan of a split (k_split_round) */
+	unsigned long long xid_stored, xid_filled; /* xid table build: requests that stored an opcode; slots that hold one */
 };
 
 struct zkb_ctx {

@@ -80,6 +80,36 @@ def test_cfg2_xidtab_from_requests(ctx, oracle, synth, zk):
     assert (g.status == 0).all()
 
 
+@pytest.mark.parametrize("seed", range(4))
+def test_xidtab_reused_xids_last_request_wins(ctx, oracle, synth, zk, seed):
+    """zcf_xidMap[xid] = opcode overwrites (zk-streams.js:145): when requests of a connection share an
+    xid the last one in stream order names the reply's opcode.  The build stores without atomics first
+    and falls back to the ordered build when a slot was written twice; both routes must agree with the
+    oracle - reused xids with different and with equal opcodes, xids outside the layout, sparse tables."""
+    import random
+    rng = random.Random(seed)
+    ops = [synth.OP[k] for k in ("CREATE", "GET_DATA", "EXISTS", "SET_DATA", "GET_CHILDREN2", "DELETE", "SYNC")]
+    c = synth.Corpus()
+    nsess = 6
+    for s in range(nsess):
+        parts = [synth.frame(synth.connect_request(rng))]
+        reuse = seed > 0 and s % 2 == 0                      # seed 0: no xid is ever reused (first route alone)
+        for i in range(rng.randrange(50, 400)):
+            xid = rng.randrange(0, 120) if reuse else 3 * i
+            op = rng.choice(ops) if seed != 2 else ops[1]     # seed 2: reused xids always carry the same opcode
+            parts.append(synth.frame(synth.be32(xid) + synth.be32(op) + synth.request_body(rng, op)))
+        c.add(b"".join(parts), server=True)
+    d, off, fl, hs = c.arrays()
+    req = ctx.decode_host(d, off, fl, hs, None)
+    req_o = oracle.decode(d, off, fl, hs, None)
+    assert req.diff(req_o) == []
+    layout = zk.XidTable(np.array([0, 5, 0, -3, 10, 0], np.int32), np.array([1300, 100, 64, 200, 0, 1200], np.uint32))
+    xt_g = ctx.xidtab_build_host(req, layout)
+    xt_o = oracle.xidtab_build(req_o, layout)
+    assert np.array_equal(xt_g.ops, xt_o.ops)
+    assert (xt_g.ops != -128).any()
+
+
 def test_cfg3_tiny(ctx, oracle, synth):
     g, o = both(ctx, oracle, synth.cfg3_tiny(50, 800))
     assert g.diff(o) == []
