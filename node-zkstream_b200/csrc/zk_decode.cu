@@ -882,6 +882,10 @@ __global__ void k_empty_sessions(uint32_t nsess, uint64_t *consumed, uint64_t *b
 /* ================================================================================== */
 /* field decode                                                                       */
 
+/* a GET_CHILDREN(2) reply whose children vector is longer than a decode tile: what k_long_children
+ * needs to walk it */
+struct LongItem { uint64_t foff; uint32_t flen, frame, brow0, srow, with_stat, chunk; };
+
 struct DecArgs {
 	const uint8_t  *bytes;
 	uint64_t        nbytes;
@@ -913,6 +917,7 @@ struct DecArgs {
 	uint4          *c_base;       /* [n_chunks] exclusive prefix of c_rows (redo passes) */
 	uint32_t        chunk0;       /* first chunk of this launch (a redo covers only the tail of a batch) */
 	uint32_t        force_exact;  /* every chunk takes the exact body (prediction switched off) */
+	struct LongItem *long_items;  /* [n_chunks] first pass: long children vectors are listed here, not walked (NULL = walk them in place) */
 	zk_ctrl        *ctrl;
 };
 
@@ -2156,6 +2161,33 @@ __global__ void __launch_bounds__(ZK_DEC_WARPS * 32, ZK_DEC_MINBLOCKS) k_decode_
 /* Exclusive prefix of the chunks' real row counts from chunk0 on, seeded with the rows before
  * chunk0 (all of which are where they belong); the totals go to the control block.  One block:
  * this only runs after a misprediction, or with the prediction switched off. */
+/* One warp per listed children vector, one tile of shared memory per warp and nothing else, so that
+ * many more of these walks are resident than the decode kernel's five CTAs per SM would allow: a
+ * single walk is a chain of dependent tile loads and short loops, and only numbers hide that.  A
+ * vector that does not keep what its header promised flags its chunk for the exact route, exactly
+ * as the decode pass does for every other frame. */
+#define ZK_LONG_WARPS 2
+#define ZK_LONG_LIST  768u     /* element offsets of one tile (an 8 KiB tile of 8..24-byte names holds about 440) */
+__global__ void __launch_bounds__(ZK_LONG_WARPS * 32) k_long_children(DecArgs a, const LongItem *items, uint32_t n)
+{
+	__shared__ __align__(128) uint8_t s_tile[ZK_LONG_WARPS][ZK_WIN + 16];
+	__shared__ __align__(8) uint64_t s_bar[ZK_LONG_WARPS];
+	__shared__ uint16_t s_list[ZK_LONG_WARPS][ZK_LONG_LIST];
+	const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+	const uint32_t i = blockIdx.x * ZK_LONG_WARPS + w;
+	if (i >= n) return;
+	if (lane == 0) mbar_init(&s_bar[w], 1);
+	__syncwarp();
+	const LongItem it = items[i];
+	const bool ok = long_children(a, s_tile[w], s_list[w], ZK_LONG_LIST, &s_bar[w], 0u, it.foff, it.flen, it.frame, it.brow0, it.srow,
+	    it.with_stat != 0, lane);
+	if (!ok && lane == 0) {
+		a.c_rows[it.chunk].x = 1u;
+		atomicOr(&a.ctrl->error, ZK_DERR_MISPREDICT);
+		atomicMin(&a.ctrl->first_bad, it.chunk);
+	}
+}
+
 __global__ void __launch_bounds__(1024) k_rows_scan(const uint4 *rows, uint4 *base, uint32_t chunk0, uint32_t n_chunks,
     uint4 seed, zk_ctrl *ctrl)
 {
@@ -2297,7 +2329,7 @@ static uint32_t zk_pick_glog2(uint64_t nbytes)
 }
 
 struct ScratchLayout {
-	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, c_rows, c_base, meta0, meta1, total;
+	size_t g_assumed, g_out, g_carry, g_cnt, g_sel, g_base, g_dirty, g_src, g_sf, g_openlocal, g_ssrc, g_sub, g_rows, g_rbase, blk, c_rows, c_base, meta0, meta1, long_items, total;
 	uint32_t glog2, n_gran, n_chunks, n_blk;
 };
 
@@ -2329,6 +2361,7 @@ static ScratchLayout zk_layout(uint64_t nbytes)
 	L.c_base = o;    o += zk_align_up((size_t)L.n_chunks * 16, 256);
 	L.meta0 = o;     o += zk_align_up((size_t)(L.n_chunks + 1) * 16, 256);
 	L.meta1 = o;     o += zk_align_up((size_t)(L.n_chunks + 1) * 16, 256);
+	L.long_items = o; o += zk_align_up((size_t)L.n_chunks * sizeof (LongItem), 256);
 	L.total = o;
 	return L;
 }
@@ -2501,7 +2534,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	uint8_t *S = (uint8_t *)ctx->d_scratch;
 	SplitArgs sa;
 	zk_fill_split_args(ctx, sa, L, d_bytes, nbytes, sess, xid);
-	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_slow, 0, sizeof (unsigned long long) * 9, ctx->stream));
+	ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->n_long, 0, sizeof (unsigned long long) * 10, ctx->stream));
 	/* sess_first_frame[nsess] = n_frames */
 	ZK_CUDA(ctx, cudaMemcpyAsync(out->sess_first_frame + nsess, &ctx->d_ctrl->n_frames, sizeof (uint32_t),
 	    cudaMemcpyDeviceToDevice, ctx->stream));
@@ -2535,11 +2568,20 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 	if (!redo) {
 		/* the ordinary pass: every chunk places its rows where the splitter predicted */
 		ZK_CUDA(ctx, cudaMemsetAsync(&ctx->d_ctrl->first_bad, 0xFF, sizeof (unsigned int), ctx->stream));
+		da.long_items = (LongItem *)(S + L.long_items);
 		if (ctx->dir == 1) k_decode<1, false><<<dec_blocks, dec_threads, 0, ctx->stream>>>(da);
 		else if (ctx->dir == 2) k_decode<2, false><<<dec_blocks, dec_threads, 0, ctx->stream>>>(da);
 		else k_decode<0, false><<<dec_blocks, dec_threads, 0, ctx->stream>>>(da);
 		LAUNCH_CHECK(ctx);
 		if ((rc = zk_read_ctrl(ctx))) return rc;
+		if (ctx->h_ctrl->n_long) {
+			/* children vectors longer than a tile were listed, not walked: their own launch */
+			const uint32_t nl = (uint32_t)ctx->h_ctrl->n_long;
+			k_long_children<<<(nl + ZK_LONG_WARPS - 1) / ZK_LONG_WARPS, ZK_LONG_WARPS * 32, 0, ctx->stream>>>(da,
+			    da.long_items, nl);
+			LAUNCH_CHECK(ctx);
+			if ((rc = zk_read_ctrl(ctx))) return rc;
+		}
 		if (ctx->h_ctrl->error == ZK_DERR_MISPREDICT) {
 			/* Some frame is not what its header promised.  Every chunk before the first one that
 			 * noticed has its rows in the right place (its own and all earlier counts matched);
@@ -2556,6 +2598,7 @@ int zk_fields_device(zkb_ctx *ctx, const uint8_t *d_bytes, uint64_t nbytes,
 			ctx->h_ctrl->n_acl = ctx->pred_rows[2];
 		}
 	}
+	da.long_items = NULL;       /* the passes below walk long vectors in place */
 	if (redo) {
 		/* exact route, no chunk waits for another: (1) the chunks the direct body could not vouch for
 		 * (all of them when the prediction is switched off) count their rows with the exact body,

@@ -464,29 +464,83 @@ __device__ __forceinline__ uint32_t walk_elems(const uint8_t *tile, uint32_t p, 
 	return p;
 }
 
-/* first position in [lo, hi) that looks like an element prefix (see above), or 0xFFFFFFFF */
-__device__ __forceinline__ uint32_t guess_elem(const uint8_t *tile, const uint32_t lo, const uint32_t hi, const uint32_t tlen)
+/* bit k set iff byte k (in address order) of the word is zero */
+__device__ __forceinline__ uint32_t zero_nib(const uint32_t w)
 {
-	for (uint32_t q = lo; q < hi && q + 4 <= tlen; ++q) {
-		const uint32_t w = sm_be32(tile, q);
-		if (w == 0 || w > 255u) continue;
-		uint32_t r = q + 4 + w;
-		bool good = true;
-#pragma unroll 1
-		for (int h = 0; h < 3 && good; ++h) {
-			if (r + 4 > tlen) break;
-			const uint32_t w2 = sm_be32(tile, r);
-			if (w2 > 255u) good = false;
-			r += 4 + w2;
-		}
-		if (good) return q;
+	const uint32_t t = ((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w;       /* bit 7 of a byte stays clear iff the byte is zero */
+	return (((~t & 0x80808080u) >> 7) * 0x01020408u) >> 24;        /* bit 8k -> bit 24 + k, no two products collide */
+}
+
+/* positions b .. b+31 (restricted to [lo, hi)) where a prefix of a string of 1..255 bytes may start:
+ * three zero bytes and a non-zero one.  b is a multiple of four. */
+__device__ __forceinline__ uint32_t elem_mask32(const uint8_t *tile, const uint32_t b, const uint32_t lo, const uint32_t hi)
+{
+	const uint32_t *wp = reinterpret_cast<const uint32_t *>(tile);
+	uint64_t Z = 0;
+#pragma unroll
+	for (int k = 0; k < 9; ++k) {
+		const uint32_t wi = (b >> 2) + (uint32_t)k;
+		const uint32_t w = wi < (ZK_WIN + 16u) / 4u ? wp[wi] : 0xffffffffu;
+		Z |= (uint64_t)zero_nib(w) << (4 * k);
 	}
-	return 0xFFFFFFFFu;
+	uint32_t cand = (uint32_t)(Z & (Z >> 1) & (Z >> 2) & ~(Z >> 3));     /* bit i: position b + i */
+	if (b < lo) cand &= 0xffffffffu << (lo - b);
+	if (hi - b < 32u) cand &= (1u << (hi - b)) - 1u;
+	return cand;
+}
+
+/* For every lane with `need`: the first position in its [lo, hi) that looks like an element prefix
+ * (see above), or 0xFFFFFFFF.  Called by the whole warp: the lanes look for their next candidate each
+ * on its own (a few mask words), then follow the three prefixes behind their candidates together -
+ * done lane by lane as each found one, that check ran at under two lanes per instruction and was
+ * nearly half of the whole walk. */
+__device__ __forceinline__ uint32_t guess_elem_warp(const uint8_t *tile, const uint32_t lo, const uint32_t hi,
+    const uint32_t tlen, const bool need)
+{
+	uint32_t b = lo & ~3u, cb = 0, cand = 0, found = 0xFFFFFFFFu;
+	bool scanning = need;
+	for (;;) {
+		uint32_t q = 0xFFFFFFFFu;
+		while (scanning && q == 0xFFFFFFFFu) {
+			if (!cand) {
+				if (b >= hi) { scanning = false; break; }
+				cand = elem_mask32(tile, b, lo, hi);
+				cb = b;
+				b += 32;
+				if (!cand) continue;
+			}
+			q = cb + (uint32_t)(__ffs((int)cand) - 1);
+			cand &= cand - 1;
+			if (q + 4 > tlen) { q = 0xFFFFFFFFu; scanning = false; }
+		}
+		__syncwarp();
+		if (!__any_sync(0xffffffffu, q != 0xFFFFFFFFu)) break;
+		bool good = q != 0xFFFFFFFFu, stop = false;
+		uint32_t r = good ? q + 4 + sm_be32(tile, q) : 0u;
+#pragma unroll
+		for (int h = 0; h < 3; ++h) {
+			if (good && !stop) {
+				if (r + 4 > tlen) stop = true;
+				else {
+					const uint32_t w2 = sm_be32(tile, r);
+					if (w2 > 255u) good = false;
+					r += 4 + w2;
+				}
+			}
+		}
+		if (q != 0xFFFFFFFFu && good) { found = q; scanning = false; }
+	}
+	return found;
 }
 
 /* `phase` is the parity of the warp's mbarrier for its next use.  Returns false if the vector or
  * the Stat behind it runs out of bytes. */
-__device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint64_t *bar, uint32_t phase,
+/* `list`: shared memory for `list_cap` tile offsets.  The rows of a tile are written from it, one
+ * element per lane in row order, so a warp's stores fall into a few sectors (written by each lane
+ * as it walks, every store instruction touched 32 sectors and the walks of a full GPU queued up
+ * behind the store path). */
+__device__ __forceinline__ bool long_children(const DecArgs &a, uint8_t *tile, uint16_t *list, const uint32_t list_cap,
+    uint64_t *bar, uint32_t phase,
     const uint64_t foff, const uint32_t flen, const uint32_t frame, const uint32_t brow0, const uint32_t srow,
     const bool with_stat, const uint32_t lane)
 {
@@ -505,7 +559,7 @@ __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint
 		if (lane == 0) {
 			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 			mbar_expect_tx(bar, tlen);
-			bulk_g2s(c.tile, a.bytes + tb, tlen, bar);
+			bulk_g2s(tile, a.bytes + tb, tlen, bar);
 		}
 		__syncwarp();
 		mbar_wait(bar, phase);
@@ -515,10 +569,12 @@ __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint
 		const uint32_t hi = (lo + ZK_LSUB < tlen) ? lo + ZK_LSUB : tlen;
 		/* first try: the lane that holds the chain's entry walks from it, the lanes after it guess */
 		uint32_t in, out, n = 0;
-		if (hi <= start || lo >= tlen) { in = out = start; }
+		const bool idle = hi <= start || lo >= tlen;
+		const uint32_t guessed = guess_elem_warp(tile, lo, hi, tlen, !idle && lo > start);
+		if (idle) { in = out = start; }
 		else {
-			in = (lo <= start) ? start : guess_elem(c.tile, lo, hi, tlen);
-			out = (in == 0xFFFFFFFFu) ? in : walk_elems<false>(c.tile, in, hi, tlen, vlim, n, 0, o, 0, 0, 0);
+			in = (lo <= start) ? start : guessed;
+			out = (in == 0xFFFFFFFFu) ? in : walk_elems<false>(tile, in, hi, tlen, vlim, n, 0, o, 0, 0, 0);
 		}
 		/* repair from the left until every lane starts where its neighbour ended */
 		for (;;) {
@@ -529,7 +585,7 @@ __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint
 			if (!wrong) break;
 			if (lane == (uint32_t)(__ffs(wrong) - 1)) {
 				in = prev;
-				out = walk_elems<false>(c.tile, in, hi, tlen, vlim, n, 0, o, 0, 0, 0);
+				out = walk_elems<false>(tile, in, hi, tlen, vlim, n, 0, o, 0, 0, 0);
 			}
 		}
 		/* rows: lane l's elements follow those of the lanes before it */
@@ -539,7 +595,29 @@ __device__ __forceinline__ bool long_children(const DecArgs &a, ChunkSm &c, uint
 		const uint32_t left = remaining > (int64_t)0x7fffffff ? 0x7fffffffu : (uint32_t)remaining;
 		const uint32_t mine = before >= left ? 0u : (left - before < n ? left - before : n);
 		uint32_t wrote = 0;
-		const uint32_t endp = walk_elems<true>(c.tile, in, hi, tlen, vlim, wrote, mine, o, row + before, frame, tb);
+		uint32_t endp;
+		if (total <= list_cap) {
+			/* the same walk once more, leaving the offsets of this lane's elements in the list */
+			uint32_t p = in, k = 0;
+			while (p < hi && p + 4 <= tlen && k < mine) {
+				const int32_t l = (int32_t)sm_be32(tile, p);
+				const uint32_t ul = l > 0 ? (uint32_t)l : 0u;
+				if (p + 4 + ul > vlim) break;
+				list[before + k] = (uint16_t)p;
+				k++;
+				p += 4 + ul;
+			}
+			endp = p;
+			__syncwarp();
+			const uint32_t emit_n = total < left ? total : left;
+			for (uint32_t j = lane; j < emit_n; j += 32) {
+				const uint32_t q = list[j];
+				const int32_t l = (int32_t)sm_be32(tile, q);
+				put_buf(o, row + j, frame, tb + q + 4, l > 0 ? l : 0);
+			}
+		} else {
+			endp = walk_elems<true>(tile, in, hi, tlen, vlim, wrote, mine, o, row + before, frame, tb);
+		}
 		/* where the chain stands after the tile: what the last lane that has bytes says */
 		const uint32_t act = __ballot_sync(0xffffffffu, lo < tlen);
 		uint32_t last_out = __shfl_sync(0xffffffffu, out, 31 - __clz((int)act));
@@ -860,7 +938,20 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 			const uint64_t lf = c.l_foff; const uint32_t ll = (uint32_t)c.l_flen, lfr = c.l_f;
 			const bool st = c.lp.n_stat != 0;
 			__syncwarp();
-			good = long_children(a, c, bar, 1u, lf, ll, lfr, e1 + rb, e0 + rs, st, lane) && good;
+			if (!REDO && a.long_items && ll > 4u * ZK_WIN) {
+				/* many tiles long: listed for k_long_children (at most one per chunk, so the list cannot
+				 * overflow); a frame that merely crosses the end of the tile is walked here */
+				if (lane == 0) {
+					LongItem it;
+					it.foff = lf; it.flen = ll; it.frame = lfr; it.brow0 = e1 + rb; it.srow = e0 + rs;
+					it.with_stat = st ? 1u : 0u; it.chunk = chunk;
+					a.long_items[atomicAdd(&a.ctrl->n_long, 1ull)] = it;
+				}
+			} else {
+				/* the work list and the frame list are free by now: they hold the element offsets */
+				good = long_children(a, c.tile, reinterpret_cast<uint16_t *>(c.vl), ZK_BM_BYTES / 2u, bar, 1u, lf, ll, lfr,
+				    e1 + rb, e0 + rs, st, lane) && good;
+			}
 		} else if (lane == 0) {
 			const Parsed p = c.lp;
 			emit_side(rd, a, c.l_foff, c.l_flen, p, c.l_f, e0 + rs, e1 + rb, e2 + ra);

@@ -33,6 +33,7 @@ struct zk_ctrl {
 	unsigned long long n_frames;
 	unsigned long long n_stat, n_buf, n_acl;
 	unsigned long long enc_bytes;
+	unsigned long long n_long;   /* children vectors longer than a tile that the decode pass left for k_long_children (cleared together with n_slow and prof) */
 	unsigned long long n_slow;   /* frames that needed the generic (exact) parser */
 	unsigned long long prof[8];  /* ZK_PROFILE_PHASES builds: cycles per decode phase, chunk count */
 	unsigned int       pred_rows[3]; /* the splitter's predicted STAT / BUF / ACL row totals of the batch */
