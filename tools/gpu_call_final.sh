@@ -18,7 +18,7 @@ BL="python bench.py --steps 2 --warmup 3 --no-cpu --no-encode --no-parity"
 $BL > $O/launch_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 130 -c 104 --csv --log-file $O/r2_launches.csv $BL > $O/ncu_launch.log 2>&1; echo "launch list rc=$?"
 # the decode kernels at full size, full set (DRAM traffic for roofline.traffic)
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:k_decode" -s 6 -c 2 -o $O/r2_kdec_10GB -f $BL > $O/ncu_kdec10.log 2>&1; echo "kdec 10GB rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^k_decode$" -s 6 -c 2 -o $O/r2_kdec_10GB -f $BL > $O/ncu_kdec10.log 2>&1; echo "kdec 10GB rc=$?"
 # every kernel family at 1 GB: launch metrics with sector efficiency
 python tools/profile_all.py 1 1 > $O/profall_plain.log 2>&1 && \
 timeout 900 ncu --metrics $M --clock-control none -k "regex:k_" -c 90 --csv --log-file $O/r2_all_metrics.csv python tools/profile_all.py 1 1 > $O/ncu_all.log 2>&1; echo "all metrics rc=$?"

@@ -1,9 +1,9 @@
 #!/bin/bash
-# Development aid: the multi-GPU call (gpurun --gpus 8).
+# Development aid: the multi-GPU call (gpurun --gpus N): bench.py re-executes itself under torch.distributed.run.
+#   tools/gpu_call_multi.sh <N> <config> [more bench.py switches]
 cd "$(dirname "$0")/.."
 O=gpurun_out
 mkdir -p $O
-B="--gpus 8 --steps 5 --warmup 3 --no-cpu --no-encode"
-timeout 900 python bench.py $B > $O/scale_cfg2_n8_compact.json 2> $O/scale_cfg2_n8_compact.err; echo "cfg2 n8 compact rc=$?"; tail -1 $O/scale_cfg2_n8_compact.json > $O/x.json; python tools/bench_brief.py $O/x.json
-timeout 900 python bench.py $B --e2e-full-columns > $O/scale_cfg2_n8_full.json 2> $O/scale_cfg2_n8_full.err; echo "cfg2 n8 full rc=$?"; tail -1 $O/scale_cfg2_n8_full.json > $O/x.json; python tools/bench_brief.py $O/x.json
-rm -f $O/x.json
+N=$1; C=$2; shift 2
+timeout 900 python bench.py --gpus $N --config $C --steps 5 --warmup 3 --no-cpu "$@" > $O/scale_${C}_n$N.json 2> $O/scale_${C}_n$N.err; echo "$C n$N rc=$?"
+tail -1 $O/scale_${C}_n$N.json > $O/x.json; python tools/bench_brief.py $O/x.json; rm -f $O/x.json
