@@ -793,10 +793,19 @@ __device__ __forceinline__ void decode_chunk_direct(const DecArgs &a, ChunkSm &c
 	do {
 		/* ---- tile offsets of frames wlo .. wlo + ZK_FREL_CAP - 1; the first window also does the
 		 * per-session bookkeeping ---- */
-		if (simple && !events && mycnt <= 8) {
+		if (simple && !events) {
 #pragma unroll
 			for (int i = 0; i < 8; ++i)
 				if ((uint32_t)i < mycnt) c.frel[lbase + i] = (uint16_t)(pk[i >> 1] >> ((i & 1) * 16));
+			if (mycnt > 8) {
+				/* more than eight frames in 256 bytes (ping replies, notifications): a plain run all the
+				 * same, followed on from the eighth */
+				uint32_t rel = pk[3] >> 16;
+				for (uint32_t i = 8; i < mycnt; ++i) {
+					rel += 4u + sm_be32(c.tile, rel);
+					c.frel[lbase + i] = (uint16_t)rel;
+				}
+			}
 		} else {
 			walk_subrange<true>(a, c, cs, hi, entry, es, esend, wlo, lbase, wlo == 0, f0 + lbase, e_start);
 		}

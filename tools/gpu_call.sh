@@ -1,6 +1,7 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
-O=gpurun_out; mkdir -p $O
-BL="python bench.py --steps 2 --warmup 3 --no-cpu --no-encode --no-parity"
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^k_decode$" -s 6 -c 2 -o $O/r2_kdec_10GB -f $BL > $O/ncu_kdec10.log 2>&1; echo "kdec 10GB rc=$?"
-ls -la $O/*.ncu-rep; du -sm $O
+P='import json,sys; d=json.loads(sys.stdin.read()); print(d["ms_per_step"], d["gpu_launches"], d["roofline"]["launch_ms"], d["roofline"]["split_ms_per_step"], round(d["roofline"]["frac"],3), d["parity"]["digest_ok"])'
+timeout 900 python -m pytest tests/test_gpu_decode_parity.py -x -q -m gpu 2>&1 | tail -1
+timeout 300 python tools/fuzz_campaign.py 1300000 600 2>&1 | tail -1
+python bench.py --config cfg3 --steps 5 --no-cpu --no-encode 2>/dev/null | tail -1 | python -c "$P"
+python bench.py --steps 5 --no-cpu --no-encode 2>/dev/null | tail -1 | python -c "$P"
