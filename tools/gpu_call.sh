@@ -1,5 +1,4 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
 P='import json,sys; d=json.loads(sys.stdin.read()); print(d["ms_per_step"], d["gpu_launches"], d["roofline"]["launch_ms"], d["roofline"]["split_ms_per_step"], round(d["roofline"]["frac"],3), d["parity"]["digest_ok"])'
-echo "== base"; python bench.py --steps 5 --no-cpu --no-encode 2>/dev/null | tail -1 | python -c "$P"
-GB=10 bash tools/variant_bench.sh sp8 sp9
+for g in 32 128; do echo "== L2 fetch $g"; ZKBATCH_L2_FETCH=$g python bench.py --steps 5 --no-cpu --no-encode 2>/tmp/err.log | tail -1 | python -c "$P"; grep -m1 "L2 fetch" /tmp/err.log; done
