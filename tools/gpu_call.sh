@@ -1,4 +1,8 @@
 #!/bin/bash
+# Development aid: the command list of one gpurun call (rewritten per experiment; started with
+# tools/run_gpu.sh).  This one: parity tests, a short differential run and the default bench line.
 cd "$(dirname "$0")/.."
-P='import json,sys; d=json.loads(sys.stdin.read()); print(d["ms_per_step"], d["gpu_launches"], d["roofline"]["launch_ms"], d["roofline"]["split_ms_per_step"], round(d["roofline"]["frac"],3), d["parity"]["digest_ok"])'
-for g in 32 128; do echo "== L2 fetch $g"; ZKBATCH_L2_FETCH=$g python bench.py --steps 5 --no-cpu --no-encode 2>/tmp/err.log | tail -1 | python -c "$P"; grep -m1 "L2 fetch" /tmp/err.log; done
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
+timeout 600 python tools/fuzz_campaign.py 300000 1000 2>&1 | tail -2
+python bench.py --steps 5 --no-cpu --no-encode 2>/dev/null | tail -1 > gpurun_out/bench_line.json
+python tools/bench_brief.py gpurun_out/bench_line.json
