@@ -243,6 +243,18 @@ __device__ __forceinline__ void enc_copy_short(EncSm &sm, const uint8_t *arena, 
 	const uint32_t n = e.dhi - e.dlo;
 	uint8_t *dp = sm.win + e.dlo;
 	const uint8_t *sp = arena + e.src;
+	if (n <= 8 && e.src + 16 <= arena_len) {
+		/* the ACL's "world" / "anyone" and the like: two or three aligned words, shifted into place,
+		 * then at most eight byte stores - no loop, no byte loads */
+		const uint32_t mis8 = (uint32_t)((uintptr_t)sp & 3u) * 8u;
+		const uint32_t *sw = reinterpret_cast<const uint32_t *>(sp - ((uintptr_t)sp & 3u));
+		const uint32_t x0 = __ldg(sw), x1 = __ldg(sw + 1), x2 = __ldg(sw + 2);
+		const uint32_t lo = __funnelshift_r(x0, x1, mis8), hi = __funnelshift_r(x1, x2, mis8);
+#pragma unroll
+		for (uint32_t k = 0; k < 8; ++k)
+			if (k < n) dp[k] = (uint8_t)((k < 4 ? lo : hi) >> ((k & 3u) * 8u));
+		return;
+	}
 	if (n < 8 || e.src + n + 8 > arena_len) {
 		for (uint32_t k = 0; k < n; ++k) dp[k] = __ldg(sp + k);
 		return;

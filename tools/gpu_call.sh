@@ -1,8 +1,6 @@
 #!/bin/bash
 # Development aid: the command list of one gpurun call (rewritten per experiment; started with
-# tools/run_gpu.sh).  This one: parity tests, a short differential run and the default bench line.
+# tools/run_gpu.sh).
 cd "$(dirname "$0")/.."
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-timeout 600 python tools/fuzz_campaign.py 300000 1000 2>&1 | tail -2
-python bench.py --steps 5 --no-cpu --no-encode 2>/dev/null | tail -1 > gpurun_out/bench_line.json
-python tools/bench_brief.py gpurun_out/bench_line.json
+timeout 600 python -m pytest tests/test_gpu_golden_and_api.py tests/test_gpu_napi_addon.py -x -q -m gpu 2>&1 | tail -1
+timeout 300 python tools/encode_bench.py 2>&1 | tail -2
