@@ -259,8 +259,17 @@ __device__ __forceinline__ void enc_copy_short(EncSm &sm, const uint8_t *arena, 
 		for (uint32_t k = 0; k < n; ++k) dp[k] = __ldg(sp + k);
 		return;
 	}
+	/* up to three bytes to the next word of the window, whole words, up to three bytes after them; the
+	 * odd bytes come out of aligned words like the rest (no byte loads, no byte loops) */
 	const uint32_t head = (4u - (e.dlo & 3u)) & 3u;
-	for (uint32_t k = 0; k < head; ++k) dp[k] = __ldg(sp + k);
+	{
+		const uint32_t m0 = (uint32_t)((uintptr_t)sp & 3u);
+		const uint32_t *s0 = reinterpret_cast<const uint32_t *>(sp - m0);
+		const uint32_t h = __funnelshift_r(__ldg(s0), __ldg(s0 + 1), m0 * 8);
+		if (head > 0) dp[0] = (uint8_t)h;
+		if (head > 1) dp[1] = (uint8_t)(h >> 8);
+		if (head > 2) dp[2] = (uint8_t)(h >> 16);
+	}
 	const uint32_t nw = (n - head) >> 2;
 	const uint32_t mis = (uint32_t)((uintptr_t)(sp + head) & 3u);
 	const uint32_t *sw = reinterpret_cast<const uint32_t *>(sp + head - mis);
@@ -272,7 +281,15 @@ __device__ __forceinline__ void enc_copy_short(EncSm &sm, const uint8_t *arena, 
 		dw[q] = mis ? __funnelshift_r(x0, x1, mis * 8) : x0;
 		x0 = mis ? x1 : __ldg(sw + q + 1);
 	}
-	for (uint32_t k = head + 4 * nw; k < n; ++k) dp[k] = __ldg(sp + k);
+	/* x0 = sw[nw]: the word the tail starts in (the read of sw[nw + 1] stays inside src + n + 8) */
+	const uint32_t rem = n - head - 4 * nw;
+	if (rem) {
+		const uint32_t t = mis ? __funnelshift_r(x0, __ldg(sw + nw + 1), mis * 8) : x0;
+		uint8_t *tp = dp + head + 4 * nw;
+		tp[0] = (uint8_t)t;
+		if (rem > 1) tp[1] = (uint8_t)(t >> 8);
+		if (rem > 2) tp[2] = (uint8_t)(t >> 16);
+	}
 }
 
 /* eight lanes copy one job: bytes [e.dlo, e.dhi) of the window from the arena */
